@@ -1,0 +1,554 @@
+// trt_api.cu -- the C ABI (include/trt_b200.h) over the CUDA kernels.  One context = one GPU.
+// There is no CPU fallback: every compute entry point runs kernels or fails with a status code.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+
+#include "trt_kernels.cuh"
+#include "trt_persistent.cuh"
+#include "trt_quantise.cuh"
+
+using namespace trt;
+
+struct trt_ctx {
+    trt_config cfg{};
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::string err;
+
+    // scene
+    trt_primitive *d_aos = nullptr;
+    float4 *d_geom = nullptr;          // ga|gb|gc|gn|mc|me, each cap_prims long
+    uint8_t *d_type = nullptr;
+    int4 *d_runs = nullptr;
+    int4 *d_lights = nullptr;
+    int *d_light_prim = nullptr;
+    float4 *d_lgeom = nullptr;         // la|lb|lc|ln|le, each cap_lights long
+    uint32_t cap_prims = 0, cap_lights = 0, cap_runs = 0;
+    SceneView sv{};
+    LightView lv{};
+    bool have_scene = false;
+    uint64_t scene_serial = 0;
+
+    // frame buffers (lib.rs:269-319: accumulation, output(pixels), variance; staging -> byte stream)
+    size_t max_pixels = 0;
+    float4 *d_pixels = nullptr, *d_accum = nullptr;
+    trt_variance *d_variance = nullptr;
+    unsigned long long *d_counters = nullptr;
+    unsigned int *d_work = nullptr;
+    uint32_t *d_row_map = nullptr;     // local row -> global row
+    uint64_t *d_row_src = nullptr;     // quantiser source offsets per output row
+    std::vector<uint32_t> rows;        // rows owned at `rows_height`
+    uint32_t rows_height = 0, rows_width = 0;
+
+    // quantiser
+    uint32_t *d_packed = nullptr, *d_block_len = nullptr;
+    uint64_t *d_block_off = nullptr;
+    uint8_t *d_stream = nullptr;
+    size_t stream_cap = 0;
+    uint64_t *h_len = nullptr;         // pinned
+    uint32_t last_q_blocks = 0;
+    bool have_stream = false;
+
+    trt_uniforms last_u{};
+    bool have_frame = false;
+    trt_timings tm{};
+    uint32_t launches = 0;
+};
+
+static thread_local std::string g_create_err;
+
+#define CK(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                            \
+            return TRT_ERR_CUDA;                                                                      \
+        }                                                                                             \
+    } while (0)
+
+static int fail(trt_ctx *ctx, int code, const char *msg) {
+    if (ctx) ctx->err = msg; else g_create_err = msg;
+    return code;
+}
+
+extern "C" const char *trt_version(void) { return "terminal-raytracer_b200 0.1 (sm_100a)"; }
+
+extern "C" const char *trt_last_error(const trt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+extern "C" void trt_destroy(trt_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
+                    ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_row_map,
+                    ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    if (ctx->h_len) cudaFreeHost(ctx->h_len);
+    for (auto &e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
+    if (!cfg || !out) return fail(nullptr, TRT_ERR_INVALID, "trt_create: null argument");
+    *out = nullptr;
+    if (cfg->abi_version != TRT_ABI_VERSION) return fail(nullptr, TRT_ERR_INVALID, "trt_create: ABI version mismatch");
+    if (cfg->max_width == 0 || cfg->max_height == 0) return fail(nullptr, TRT_ERR_INVALID, "trt_create: zero frame size");
+    if (cfg->conv > 1u) return fail(nullptr, TRT_ERR_INVALID, "trt_create: unknown arithmetic convention");
+    if (cfg->shard_count > 1u && cfg->shard_index >= cfg->shard_count)
+        return fail(nullptr, TRT_ERR_INVALID, "trt_create: shard_index >= shard_count");
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0) {
+        g_create_err = std::string("trt_create: no CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback";
+        cudaGetLastError();
+        return TRT_ERR_NO_DEVICE;
+    }
+    if (cfg->device < 0 || cfg->device >= n_dev) return fail(nullptr, TRT_ERR_INVALID, "trt_create: bad device ordinal");
+    trt_ctx *ctx = new (std::nothrow) trt_ctx();
+    if (!ctx) return fail(nullptr, TRT_ERR_NOMEM, "trt_create: out of host memory");
+    ctx->cfg = *cfg;
+    if (ctx->cfg.shard_count == 0) ctx->cfg.shard_count = 1;
+    if (ctx->cfg.stripe_rows == 0) ctx->cfg.stripe_rows = 1;
+    ctx->device = cfg->device;
+    int rc = [&]() -> int {
+        CK(cudaSetDevice(ctx->device));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, ctx->device));
+        ctx->sm_count = prop.multiProcessorCount;
+        CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        for (auto &ev : ctx->ev) CK(cudaEventCreate(&ev));
+        ctx->max_pixels = (size_t)cfg->max_width * cfg->max_height;
+        CK(cudaMalloc(&ctx->d_pixels, ctx->max_pixels * sizeof(float4)));
+        CK(cudaMalloc(&ctx->d_accum, ctx->max_pixels * sizeof(float4)));
+        CK(cudaMalloc(&ctx->d_variance, ctx->max_pixels * sizeof(trt_variance)));
+        CK(cudaMemsetAsync(ctx->d_pixels, 0, ctx->max_pixels * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->d_accum, 0, ctx->max_pixels * sizeof(float4), ctx->stream));
+        CK(cudaMemsetAsync(ctx->d_variance, 0, ctx->max_pixels * sizeof(trt_variance), ctx->stream));
+        CK(cudaMalloc(&ctx->d_counters, K_COUNT * sizeof(unsigned long long)));
+        CK(cudaMemsetAsync(ctx->d_counters, 0, K_COUNT * sizeof(unsigned long long), ctx->stream));
+        CK(cudaMalloc(&ctx->d_work, 64));
+        CK(cudaMalloc(&ctx->d_row_map, (size_t)cfg->max_height * sizeof(uint32_t)));
+        CK(cudaMalloc(&ctx->d_row_src, (size_t)cfg->max_height * sizeof(uint64_t)));
+        CK(cudaMalloc(&ctx->d_packed, ctx->max_pixels * sizeof(uint32_t)));
+        const size_t nb = (ctx->max_pixels + TRT_Q_BLOCK - 1) / TRT_Q_BLOCK;
+        CK(cudaMalloc(&ctx->d_block_len, nb * sizeof(uint32_t)));
+        CK(cudaMalloc(&ctx->d_block_off, (nb + 1) * sizeof(uint64_t)));
+        ctx->stream_cap = ctx->max_pixels * 26 + (size_t)cfg->max_height * 2 + 64;
+        CK(cudaMalloc(&ctx->d_stream, ctx->stream_cap));
+        CK(cudaMallocHost(&ctx->h_len, 64));
+        CK(cudaStreamSynchronize(ctx->stream));
+        return TRT_OK;
+    }();
+    if (rc != TRT_OK) {
+        g_create_err = ctx->err;
+        trt_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return TRT_OK;
+}
+
+// ---- scene ------------------------------------------------------------------------------------------
+extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32_t count) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (!prims && count) return fail(ctx, TRT_ERR_INVALID, "trt_upload_scene: null primitives");
+    CK(cudaSetDevice(ctx->device));
+    // host-side index structures: type runs and the light list, in scan order (lib.rs:122-154 push order)
+    std::vector<uint8_t> types(count);
+    std::vector<int4> runs;
+    std::vector<int> light_prim;
+    for (uint32_t i = 0; i < count; i++) {
+        const uint32_t t = prims[i].primitive_type;
+        types[i] = t <= 2u ? (uint8_t)t : (uint8_t)255;
+        if (runs.empty() || runs.back().x != (int)types[i]) runs.push_back(make_int4((int)types[i], (int)i, (int)i + 1, 0));
+        else runs.back().z = (int)i + 1;
+        // shader.wgsl:346-347 light test, :352/:370 supported light types
+        const float power = prims[i].emission.x + prims[i].emission.y + prims[i].emission.z;
+        if (power > 0.001f && (t == 0u || t == 2u)) light_prim.push_back((int)i);
+    }
+    const uint32_t n_lights = (uint32_t)light_prim.size(), n_runs = (uint32_t)runs.size();
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (count > ctx->cap_prims) {
+        if (ctx->d_aos) { cudaFree(ctx->d_aos); cudaFree(ctx->d_geom); cudaFree(ctx->d_type); }
+        ctx->d_aos = nullptr; ctx->d_geom = nullptr; ctx->d_type = nullptr; ctx->cap_prims = 0;
+        const uint32_t cap = count < 64u ? 64u : count;
+        CK(cudaMalloc(&ctx->d_aos, (size_t)cap * sizeof(trt_primitive)));
+        CK(cudaMalloc(&ctx->d_geom, (size_t)cap * 6 * sizeof(float4)));
+        CK(cudaMalloc(&ctx->d_type, cap));
+        ctx->cap_prims = cap;
+    }
+    if (n_lights > ctx->cap_lights || !ctx->d_lgeom) {
+        if (ctx->d_lgeom) { cudaFree(ctx->d_lgeom); cudaFree(ctx->d_light_prim); cudaFree(ctx->d_lights); }
+        ctx->d_lgeom = nullptr; ctx->d_light_prim = nullptr; ctx->d_lights = nullptr; ctx->cap_lights = 0;
+        const uint32_t cap = n_lights < 16u ? 16u : n_lights;
+        CK(cudaMalloc(&ctx->d_lgeom, (size_t)cap * 5 * sizeof(float4)));
+        CK(cudaMalloc(&ctx->d_light_prim, (size_t)cap * sizeof(int)));
+        CK(cudaMalloc(&ctx->d_lights, (size_t)cap * sizeof(int4)));
+        ctx->cap_lights = cap;
+    }
+    if (n_runs > ctx->cap_runs || !ctx->d_runs) {
+        if (ctx->d_runs) cudaFree(ctx->d_runs);
+        ctx->d_runs = nullptr; ctx->cap_runs = 0;
+        const uint32_t cap = n_runs < 16u ? 16u : n_runs;
+        CK(cudaMalloc(&ctx->d_runs, (size_t)cap * sizeof(int4)));
+        ctx->cap_runs = cap;
+    }
+    if (count) {
+        CK(cudaMemcpyAsync(ctx->d_aos, prims, (size_t)count * sizeof(trt_primitive), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->d_type, types.data(), count, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->d_runs, runs.data(), n_runs * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (n_lights)
+        CK(cudaMemcpyAsync(ctx->d_light_prim, light_prim.data(), n_lights * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    const size_t cp = ctx->cap_prims, cl = ctx->cap_lights;
+    RepackParams rp{};
+    rp.aos = ctx->d_aos; rp.n_prims = (int)count;
+    rp.ga = ctx->d_geom; rp.gb = ctx->d_geom + cp; rp.gc = ctx->d_geom + 2 * cp; rp.gn = ctx->d_geom + 3 * cp;
+    rp.mc = ctx->d_geom + 4 * cp; rp.me = ctx->d_geom + 5 * cp;
+    rp.light_prim = ctx->d_light_prim; rp.n_lights = (int)n_lights;
+    rp.la = ctx->d_lgeom; rp.lb = ctx->d_lgeom + cl; rp.lc = ctx->d_lgeom + 2 * cl; rp.ln = ctx->d_lgeom + 3 * cl;
+    rp.le = ctx->d_lgeom + 4 * cl;
+    const uint32_t work = count > n_lights ? count : n_lights;
+    if (work) {
+        if (ctx->cfg.conv) repack_kernel<1><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
+        else repack_kernel<0><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
+        CK(cudaGetLastError());
+    }
+    ctx->sv.ga = rp.ga; ctx->sv.gb = rp.gb; ctx->sv.gc = rp.gc; ctx->sv.gn = rp.gn; ctx->sv.mc = rp.mc; ctx->sv.me = rp.me;
+    ctx->sv.type = ctx->d_type; ctx->sv.runs = ctx->d_runs; ctx->sv.lights = ctx->d_lights;
+    ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;
+    ctx->lv.la = rp.la; ctx->lv.lb = rp.lb; ctx->lv.lc = rp.lc; ctx->lv.ln = rp.ln; ctx->lv.le = rp.le;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(persistent_scene_upload(ctx->sv, ctx->lv, ctx->stream));
+    ctx->have_scene = true;
+    ctx->scene_serial++;
+    return TRT_OK;
+}
+
+// ---- frame -------------------------------------------------------------------------------------------
+// rows owned by this shard at frame height h: stripes of stripe_rows rows dealt round-robin
+static void shard_rows(const trt_config &c, uint32_t h, std::vector<uint32_t> &rows) {
+    rows.clear();
+    for (uint32_t y = 0; y < h; y++) {
+        const uint32_t stripe = y / c.stripe_rows;
+        if (c.shard_count <= 1u || stripe % c.shard_count == c.shard_index) rows.push_back(y);
+    }
+}
+
+extern "C" uint32_t trt_shard_rows(const trt_ctx *ctx, uint32_t height, uint32_t *rows, uint32_t cap) {
+    if (!ctx) return 0;
+    std::vector<uint32_t> r;
+    shard_rows(ctx->cfg, height, r);
+    for (uint32_t i = 0; i < r.size() && i < cap && rows; i++) rows[i] = r[i];
+    return (uint32_t)r.size();
+}
+
+static int ensure_rows(trt_ctx *ctx, uint32_t w, uint32_t h) {
+    if (ctx->rows_height == h && ctx->rows_width == w) return TRT_OK;
+    shard_rows(ctx->cfg, h, ctx->rows);
+    std::vector<uint64_t> src(ctx->rows.size());
+    for (size_t i = 0; i < ctx->rows.size(); i++) src[i] = (uint64_t)ctx->rows[i] * w;
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (!ctx->rows.empty()) {
+        CK(cudaMemcpy(ctx->d_row_map, ctx->rows.data(), ctx->rows.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(ctx->d_row_src, src.data(), src.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    }
+    ctx->rows_height = h;
+    ctx->rows_width = w;
+    return TRT_OK;
+}
+
+static int check_uniforms(trt_ctx *ctx, const trt_uniforms *u) {
+    if (!u) return fail(ctx, TRT_ERR_INVALID, "null uniforms");
+    if (!ctx->have_scene) return fail(ctx, TRT_ERR_NO_SCENE, "render before trt_upload_scene");
+    if (u->width == 0 || u->height == 0 || u->width > ctx->cfg.max_width || u->height > ctx->cfg.max_height ||
+        (size_t)u->width * u->height > ctx->max_pixels)
+        return fail(ctx, TRT_ERR_INVALID, "uniforms: frame size is zero or exceeds trt_config.max_width/max_height");
+    if (u->primitive_count > (uint32_t)ctx->sv.n_prims)
+        return fail(ctx, TRT_ERR_INVALID, "uniforms: primitive_count exceeds the uploaded scene");
+    return TRT_OK;
+}
+
+extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
+    if (!ctx) return TRT_ERR_INVALID;
+    int rc = check_uniforms(ctx, u);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    if (u->primitive_count != (uint32_t)ctx->sv.n_prims)
+        return fail(ctx, TRT_ERR_INVALID, "uniforms: primitive_count must equal the uploaded primitive count");
+    rc = ensure_rows(ctx, u->width, u->height);
+    if (rc) return rc;
+    FrameParams fp{};
+    fp.width = u->width; fp.height = u->height; fp.spp = u->samples_per_pixel; fp.max_depth = u->max_depth;
+    fp.seed = u->seed; fp.frame_number = u->frame_number;
+    fp.base_samples = u->samples_per_pixel / 4u < 4u ? 4u : u->samples_per_pixel / 4u;     // shader.wgsl:513
+    fp.n_local_pixels = (uint32_t)(ctx->rows.size() * (size_t)u->width);
+    fp.char_aspect = u->char_aspect_ratio;
+    fp.half_h = tanf(u->fov_rad / 2.0f);                 // shader.wgsl:522, frame-uniform: evaluated once (glibc)
+    fp.half_w = u->aspect_ratio * fp.half_h;             // shader.wgsl:523
+    fp.wm1 = (float)(u->width - 1u);
+    fp.hm1 = (float)(u->height - 1u);
+    fp.spp_f = (float)u->samples_per_pixel;
+    fp.base_f = (float)fp.base_samples;
+    fp.cam_pos = make_float3(u->camera_pos.x, u->camera_pos.y, u->camera_pos.z);
+    fp.cam_fwd = make_float3(u->camera_forward.x, u->camera_forward.y, u->camera_forward.z);
+    fp.cam_right = make_float3(u->camera_right.x, u->camera_right.y, u->camera_right.z);
+    fp.cam_up = make_float3(u->camera_up.x, u->camera_up.y, u->camera_up.z);
+    fp.row_map = ctx->cfg.shard_count > 1u ? ctx->d_row_map : nullptr;
+    fp.pixels = ctx->d_pixels; fp.accumulation = ctx->d_accum; fp.variance = ctx->d_variance;
+    fp.counters = ctx->d_counters; fp.work_counter = ctx->d_work;
+    ctx->launches = 0;
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    if (fp.n_local_pixels) {
+        if (ctx->cfg.count_work) {
+            const uint32_t blocks = (fp.n_local_pixels + 127u) / 128u;
+            if (ctx->cfg.conv) trace_pixel_kernel<1, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
+            else trace_pixel_kernel<0, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
+            ctx->launches += 1;
+        } else {
+            cudaError_t e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream,
+                                                    &ctx->launches);
+            if (e != cudaSuccess) { ctx->err = std::string("trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
+        }
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    ctx->last_u = *u;
+    ctx->have_frame = true;
+    return TRT_OK;
+}
+
+static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_src, uint32_t w, uint32_t rows, int mode) {
+    if (mode != TRT_MODE_ASCII && mode != TRT_MODE_TRUECOLOR) return fail(ctx, TRT_ERR_INVALID, "quantise: bad mode");
+    const uint64_t n = (uint64_t)w * rows;
+    if (n > ctx->max_pixels) return fail(ctx, TRT_ERR_INVALID, "quantise: frame exceeds the context's capacity");
+    QuantParams q{};
+    q.src = src; q.row_src = row_src; q.width = w; q.height = rows; q.mode = mode;
+    q.packed = ctx->d_packed; q.block_len = ctx->d_block_len; q.block_off = ctx->d_block_off;
+    q.n_blocks = (uint32_t)((n + TRT_Q_BLOCK - 1) / TRT_Q_BLOCK);
+    q.out = ctx->d_stream; q.out_cap = ctx->stream_cap;
+    if (q.n_blocks) {
+        quant_pack_kernel<<<q.n_blocks, TRT_Q_BLOCK, 0, ctx->stream>>>(q);
+        quant_scan_kernel<<<1, 1024, 0, ctx->stream>>>(q);
+        quant_emit_kernel<<<q.n_blocks, TRT_Q_BLOCK, 0, ctx->stream>>>(q);
+        ctx->launches += 3;
+        CK(cudaGetLastError());
+    } else {
+        CK(cudaMemsetAsync(ctx->d_block_off, 0, sizeof(uint64_t), ctx->stream));
+    }
+    ctx->last_q_blocks = q.n_blocks;
+    CK(cudaMemcpyAsync(ctx->h_len, ctx->d_block_off + q.n_blocks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->have_stream = true;
+    return TRT_OK;
+}
+
+extern "C" int trt_quantise_async(trt_ctx *ctx, int mode, size_t *len_needed) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (!ctx->have_frame) return fail(ctx, TRT_ERR_INVALID, "quantise before any frame was traced");
+    CK(cudaSetDevice(ctx->device));
+    const bool sharded = ctx->cfg.shard_count > 1u;
+    int rc = launch_quantise(ctx, ctx->d_pixels, sharded ? ctx->d_row_src : nullptr, ctx->last_u.width,
+                             (uint32_t)ctx->rows.size(), mode);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    if (len_needed) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        *len_needed = (size_t)*ctx->h_len;
+    }
+    return TRT_OK;
+}
+
+extern "C" int trt_quantise_gathered(trt_ctx *ctx, const void *d_gathered, size_t block_stride_bytes, uint32_t width,
+                                     uint32_t height, uint32_t shard_count, uint32_t stripe_rows, int mode,
+                                     size_t *len_needed) {
+    if (!ctx || !d_gathered || !width || !height || !shard_count || !stripe_rows) return fail(ctx, TRT_ERR_INVALID, "quantise_gathered: bad argument");
+    if (height > ctx->cfg.max_height || (size_t)width * height > ctx->max_pixels || block_stride_bytes % sizeof(float4))
+        return fail(ctx, TRT_ERR_INVALID, "quantise_gathered: frame exceeds the context's capacity");
+    CK(cudaSetDevice(ctx->device));
+    // global row y lives in block (stripe % shard_count) at local row index = (rows of that shard below y)
+    std::vector<uint64_t> src(height);
+    std::vector<uint32_t> local(shard_count, 0);
+    for (uint32_t y = 0; y < height; y++) {
+        const uint32_t owner = (y / stripe_rows) % shard_count;
+        src[y] = (uint64_t)owner * (block_stride_bytes / sizeof(float4)) + (uint64_t)local[owner] * width;
+        local[owner]++;
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(ctx->d_row_src, src.data(), height * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    ctx->rows_height = 0;      // d_row_src no longer describes this shard's rows
+    ctx->launches = 0;
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    int rc = launch_quantise(ctx, (const float4 *)d_gathered, ctx->d_row_src, width, height, mode);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    if (len_needed) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        *len_needed = (size_t)*ctx->h_len;
+    }
+    return TRT_OK;
+}
+
+extern "C" int trt_sync(trt_ctx *ctx) {
+    if (!ctx) return TRT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return TRT_OK;
+}
+
+extern "C" int trt_read_stream(trt_ctx *ctx, uint8_t *out, size_t cap, size_t *len) {
+    if (!ctx || !len) return TRT_ERR_INVALID;
+    if (!ctx->have_stream) return fail(ctx, TRT_ERR_INVALID, "read_stream before quantise");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const size_t n = (size_t)*ctx->h_len;
+    *len = n;
+    if (n > ctx->stream_cap) return fail(ctx, TRT_ERR_INVALID, "internal: stream longer than its buffer");
+    if (n > cap || (!out && n)) return fail(ctx, TRT_ERR_TOO_SMALL, "output buffer too small for the frame stream");
+    if (n) CK(cudaMemcpyAsync(out, ctx->d_stream, n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return TRT_OK;
+}
+
+extern "C" int trt_render_frame(trt_ctx *ctx, const trt_uniforms *u, int mode, uint8_t *out, size_t cap, size_t *len) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (mode != TRT_MODE_ASCII && mode != TRT_MODE_TRUECOLOR && mode != TRT_MODE_NONE)
+        return fail(ctx, TRT_ERR_INVALID, "render_frame: bad mode");
+    int rc = trt_trace_async(ctx, u);
+    if (rc) return rc;
+    if (mode == TRT_MODE_NONE) {
+        if (len) *len = 0;
+        CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+        CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+        return trt_sync(ctx);
+    }
+    rc = trt_quantise_async(ctx, mode, nullptr);
+    if (rc) return rc;
+    size_t n = 0;
+    rc = trt_read_stream(ctx, out, cap, &n);
+    if (len) *len = n;
+    return rc;
+}
+
+extern "C" int trt_get_timings(trt_ctx *ctx, trt_timings *out) {
+    if (!ctx || !out) return TRT_ERR_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    trt_timings t{};
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) t.trace_ms = ms;
+    if (cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2]) == cudaSuccess) t.quantise_ms = ms;
+    if (cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]) == cudaSuccess) t.d2h_ms = ms;
+    if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[3]) == cudaSuccess) t.total_ms = ms;
+    cudaGetLastError();
+    t.kernel_launches = ctx->launches;
+    *out = t;
+    return TRT_OK;
+}
+
+// ---- parity / checkpoint access ---------------------------------------------------------------------
+// Copies the rows this shard owns from a full-frame device buffer into the caller's full-frame array.
+static int read_rows(trt_ctx *ctx, const void *d_src, void *dst, size_t elem, size_t n_pixels) {
+    if (!ctx->have_frame) return fail(ctx, TRT_ERR_INVALID, "read before any frame was traced");
+    const size_t w = ctx->last_u.width, h = ctx->last_u.height;
+    if (!dst || n_pixels < w * h) return fail(ctx, TRT_ERR_TOO_SMALL, "read: destination smaller than width*height");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->cfg.shard_count <= 1u) {
+        CK(cudaMemcpy(dst, d_src, w * h * elem, cudaMemcpyDeviceToHost));
+        return TRT_OK;
+    }
+    std::vector<uint32_t> rows;
+    shard_rows(ctx->cfg, (uint32_t)h, rows);
+    for (uint32_t y : rows)
+        CK(cudaMemcpy((char *)dst + (size_t)y * w * elem, (const char *)d_src + (size_t)y * w * elem, w * elem,
+                      cudaMemcpyDeviceToHost));
+    return TRT_OK;
+}
+
+extern "C" int trt_read_pixels(trt_ctx *ctx, float *dst4, size_t n_pixels) {
+    if (!ctx) return TRT_ERR_INVALID;
+    return read_rows(ctx, ctx->d_pixels, dst4, sizeof(float4), n_pixels);
+}
+extern "C" int trt_read_accumulation(trt_ctx *ctx, float *dst4, size_t n_pixels) {
+    if (!ctx) return TRT_ERR_INVALID;
+    return read_rows(ctx, ctx->d_accum, dst4, sizeof(float4), n_pixels);
+}
+extern "C" int trt_read_variance(trt_ctx *ctx, trt_variance *dst, size_t n_pixels) {
+    if (!ctx) return TRT_ERR_INVALID;
+    return read_rows(ctx, ctx->d_variance, dst, sizeof(trt_variance), n_pixels);
+}
+extern "C" int trt_write_accumulation(trt_ctx *ctx, const float *src4, size_t n_pixels) {
+    if (!ctx || !src4) return TRT_ERR_INVALID;
+    if (n_pixels > ctx->max_pixels) return fail(ctx, TRT_ERR_INVALID, "write_accumulation: more pixels than the context holds");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(ctx->d_accum, src4, n_pixels * sizeof(float4), cudaMemcpyHostToDevice));
+    return TRT_OK;
+}
+
+extern "C" int trt_get_counters(trt_ctx *ctx, trt_counters *out) {
+    if (!ctx || !out) return TRT_ERR_INVALID;
+    static_assert(sizeof(trt_counters) == K_COUNT * sizeof(unsigned long long), "counter layout");
+    if (!ctx->cfg.count_work) return fail(ctx, TRT_ERR_INVALID, "counters need trt_config.count_work = 1");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->d_counters, sizeof(trt_counters), cudaMemcpyDeviceToHost));
+    CK(cudaMemset(ctx->d_counters, 0, sizeof(trt_counters)));      // counters are per read interval
+    return TRT_OK;
+}
+
+// ---- multi-GPU plumbing -------------------------------------------------------------------------------
+extern "C" int trt_device_buffer(trt_ctx *ctx, int which, void **dptr, size_t *bytes) {
+    if (!ctx || !dptr) return TRT_ERR_INVALID;
+    size_t n = 0;
+    switch (which) {
+        case 0: *dptr = ctx->d_pixels; n = ctx->max_pixels * sizeof(float4); break;
+        case 1: *dptr = ctx->d_accum; n = ctx->max_pixels * sizeof(float4); break;
+        case 2: *dptr = ctx->d_variance; n = ctx->max_pixels * sizeof(trt_variance); break;
+        case 3: *dptr = ctx->d_stream; n = ctx->stream_cap; break;
+        default: return fail(ctx, TRT_ERR_INVALID, "device_buffer: unknown buffer id");
+    }
+    if (bytes) *bytes = n;
+    return TRT_OK;
+}
+
+extern "C" int trt_cuda_stream(trt_ctx *ctx, void **stream) {
+    if (!ctx || !stream) return TRT_ERR_INVALID;
+    *stream = (void *)ctx->stream;
+    return TRT_OK;
+}
+
+extern "C" int trt_pack_shard_pixels(trt_ctx *ctx, void *d_dst, size_t dst_bytes) {
+    if (!ctx || !d_dst) return TRT_ERR_INVALID;
+    if (!ctx->have_frame) return fail(ctx, TRT_ERR_INVALID, "pack before any frame was traced");
+    CK(cudaSetDevice(ctx->device));
+    int rc = ensure_rows(ctx, ctx->last_u.width, ctx->last_u.height);
+    if (rc) return rc;
+    const uint32_t n = (uint32_t)(ctx->rows.size() * (size_t)ctx->last_u.width);
+    if ((size_t)n * sizeof(float4) > dst_bytes) return fail(ctx, TRT_ERR_TOO_SMALL, "pack: destination too small");
+    if (n) {
+        pack_rows_kernel<<<(n + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->d_pixels, (float4 *)d_dst,
+                                                                     ctx->cfg.shard_count > 1u ? ctx->d_row_map : nullptr,
+                                                                     ctx->last_u.width, n);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+    }
+    return TRT_OK;
+}
+
+extern "C" int trt_alloc_host(size_t bytes, void **out) {
+    if (!out) return TRT_ERR_INVALID;
+    *out = nullptr;
+    cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+    if (e != cudaSuccess) { g_create_err = std::string("trt_alloc_host: ") + cudaGetErrorString(e); cudaGetLastError(); return TRT_ERR_CUDA; }
+    return TRT_OK;
+}
+extern "C" void trt_free_host(void *p) { if (p) cudaFreeHost(p); }

@@ -1,0 +1,161 @@
+// trt_device.cuh -- device-side data layout and math of the sm_100a path tracer.
+//
+// Written from scratch for B200; behaviour follows /root/reference/src/shader.wgsl (cited per
+// function).  This translation unit is compiled with --fmad=false: nvcc never contracts a*b+c on
+// its own, so TRT_CONV_AS_WRITTEN is one IEEE rounding per WGSL operator, and TRT_CONV_FUSED fuses
+// exactly where __fmaf_rn is written below (DESIGN.md "Arithmetic conventions").
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/trt_b200.h"
+
+namespace trt {
+
+// ---- scene in HBM: structure of arrays, one float4 per field per primitive ----------------------
+// (the reference scans a 180-byte AoS struct per test, shader.wgsl:255; here a test touches 32-48 B)
+//   sphere   : ga = (cx, cy, cz, r)     gb = (r*r, -, -, -)
+//   plane    : ga = (px, py, pz, -)     gb = (nx, ny, nz, -) raw     gn = normalize(n)
+//   triangle : ga = v0                  gb = e1 = v1-v0   gc = e2 = v2-v0   gn = normalize(e1 x e2)
+// material   : mc = (color.rgb, reflectivity)   me = (emission.rgb, type as float bits)
+// Every derived value (r*r, e1, e2, normals, light area) is computed with the same f32 operation
+// sequence the shader uses, so it is bit-identical to recomputing it per test.
+struct SceneView {
+    const float4 *ga, *gb, *gc, *gn, *mc, *me;
+    const uint8_t *type;        // per primitive: 0 sphere, 1 plane, 2 triangle, 255 unknown
+    const int4 *runs;           // (type, begin, end, -) maximal runs of equal type, in scan order
+    const int4 *lights;         // (prim index, type, area as float bits, -) emissive spheres/triangles in scan order
+    int n_prims, n_runs, n_lights;
+};
+
+#define TRT_CONST_PRIMS 256     // scenes up to this size are also mirrored in __constant__ memory
+
+struct FrameParams {
+    uint32_t width, height, spp, max_depth;
+    uint32_t seed, frame_number, base_samples, n_local_pixels;
+    float inv_unused, char_aspect, half_h, half_w;      // half_h = tan(fov/2) (host, glibc), half_w = aspect*half_h
+    float wm1, hm1;                                     // f32(width-1), f32(height-1)
+    float spp_f, base_f;
+    float3 cam_pos, cam_fwd, cam_right, cam_up;
+    const uint32_t *row_map;     // local row -> global row (row sharding); NULL = identity
+    float4 *pixels, *accumulation;
+    trt_variance *variance;
+    unsigned long long *counters;   // trt_counters as 19 x u64 (instrumented build only)
+    unsigned int *work_counter;     // persistent kernel: next pixel to hand out
+};
+
+__device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
+__device__ __forceinline__ float3 xyz(float4 v) { return make_float3(v.x, v.y, v.z); }
+
+// ---- vector helpers (shader.wgsl:83-101,126-140,225-232) ----------------------------------------
+template <int CONV> struct M {
+    static __device__ __forceinline__ float3 add(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+    static __device__ __forceinline__ float3 sub(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+    static __device__ __forceinline__ float3 scale(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+    static __device__ __forceinline__ float3 mulv(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+    static __device__ __forceinline__ float3 divs(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+    static __device__ __forceinline__ float dot(float3 a, float3 b) {
+        if (CONV) return __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, a.x * b.x));
+        return a.x * b.x + a.y * b.y + a.z * b.z;
+    }
+    static __device__ __forceinline__ float3 cross(float3 a, float3 b) {
+        if (CONV) return f3(__fmaf_rn(a.y, b.z, -(a.z * b.y)), __fmaf_rn(a.z, b.x, -(a.x * b.z)), __fmaf_rn(a.x, b.y, -(a.y * b.x)));
+        return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+    }
+    static __device__ __forceinline__ float3 axpy(float3 a, float3 b, float s) {          // a + b*s
+        if (CONV) return f3(__fmaf_rn(b.x, s, a.x), __fmaf_rn(b.y, s, a.y), __fmaf_rn(b.z, s, a.z));
+        return f3(a.x + b.x * s, a.y + b.y * s, a.z + b.z * s);
+    }
+    static __device__ __forceinline__ float3 vmad(float3 a, float3 b, float3 c) {         // a + b*c
+        if (CONV) return f3(__fmaf_rn(b.x, c.x, a.x), __fmaf_rn(b.y, c.y, a.y), __fmaf_rn(b.z, c.z, a.z));
+        return f3(a.x + b.x * c.x, a.y + b.y * c.y, a.z + b.z * c.z);
+    }
+    static __device__ __forceinline__ float3 lin3(float3 a, float s, float3 b, float t, float3 c, float u) {
+        if (CONV)
+            return f3(__fmaf_rn(c.x, u, __fmaf_rn(b.x, t, a.x * s)), __fmaf_rn(c.y, u, __fmaf_rn(b.y, t, a.y * s)),
+                      __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
+        return f3(a.x * s + b.x * t + c.x * u, a.y * s + b.y * t + c.y * u, a.z * s + b.z * t + c.z * u);
+    }
+    static __device__ __forceinline__ float length(float3 v) { return sqrtf(dot(v, v)); }
+    static __device__ __forceinline__ float3 normalize(float3 v) { return divs(v, length(v)); }
+    static __device__ __forceinline__ float3 reflect(float3 v, float3 n) {                 // shader.wgsl:138-140
+        float k = 2.0f * dot(v, n);
+        if (CONV) return f3(__fmaf_rn(n.x, -k, v.x), __fmaf_rn(n.y, -k, v.y), __fmaf_rn(n.z, -k, v.z));
+        return sub(v, scale(n, k));
+    }
+    static __device__ __forceinline__ float msub(float a, float b, float c) {              // a*b - c
+        if (CONV) return __fmaf_rn(a, b, -c);
+        return a * b - c;
+    }
+    static __device__ __forceinline__ float nmadd(float c, float a, float b) {             // c - a*b
+        if (CONV) return __fmaf_rn(-a, b, c);
+        return c - a * b;
+    }
+};
+
+// ---- RNG (shader.wgsl:104-115) --------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pcg_hash(uint32_t input) {
+    uint32_t state = input * 747796405u + 2891336453u;
+    uint32_t word = ((state >> ((state >> 28u) + 4u)) ^ state) * 277803737u;
+    return (word >> 22u) ^ word;
+}
+// f32(state) / 4294967295.0: the literal is 2^32 in f32, so this is an exact scaling by 2^-32
+__device__ __forceinline__ float rnd(uint32_t &state) {
+    state = pcg_hash(state);
+    return __uint2float_rn(state) * 2.3283064365386963e-10f;
+}
+
+// ---- pinned sin/cos: the arithmetic convention for WGSL sin()/cos() --------------------
+// Cody-Waite reduction by pi/2 in three fused steps, degree-7/8 minimax polynomials, all fused.
+__device__ __forceinline__ void sincos_pinned(float phi, float &sn, float &cs) {
+    float q = rintf(phi * 0.6366197466850281f);
+    float r = __fmaf_rn(q, -1.5703125f, phi);
+    r = __fmaf_rn(q, -0.0004837512969970703f, r);
+    r = __fmaf_rn(q, -7.549790126404332e-08f, r);
+    float s = r * r;
+    float ps = __fmaf_rn(-0.00019517233886290342f, s, 0.008332177996635437f);
+    ps = __fmaf_rn(ps, s, -0.16666655242443085f);
+    float sr = __fmaf_rn(r * s, ps, r);
+    float pc = __fmaf_rn(2.4438379114144482e-05f, s, -0.0013887366512790322f);
+    pc = __fmaf_rn(pc, s, 0.04166664555668831f);
+    pc = __fmaf_rn(pc, s, -0.5f);
+    float cr = __fmaf_rn(pc, s, 1.0f);
+    int k = __float2int_rn(q) & 3;
+    float so = (k & 1) ? cr : sr;
+    float co = (k & 1) ? sr : cr;
+    if (k == 1 || k == 2) co = -co;
+    if (k >= 2) so = -so;
+    sn = so;
+    cs = co;
+}
+
+#define TRT_PI_F 3.14159265359f
+#define TRT_TWO_PI_F 6.28318530718f
+#define TRT_FOUR_PI_F 12.56637061436f
+
+// ---- counters -----------------------------------------------------------------------------------------
+enum {
+    K_PIXELS, K_SAMPLES_BASE, K_SAMPLES_EXTRA, K_CLOSEST_SCANS, K_HITS, K_MISSES, K_SHADOW_SCANS,
+    K_SHADOW_UNOCCLUDED, K_SHADOW_LIT, K_SHADOW_NEEDED, K_MIRROR, K_DIFFUSE, K_ROULETTE_TESTS,
+    K_ROULETTE_KILLS, K_PRIM_TESTS, K_PRIM_TESTS_MIN, K_FLOPS_WRITTEN, K_FLOPS_MIN, K_RNG_DRAWS, K_COUNT
+};
+template <bool COUNT> struct Counters;
+template <> struct Counters<false> {
+    __device__ __forceinline__ void add(int, uint32_t) {}
+    __device__ __forceinline__ void flops(uint32_t) {}          // written and min
+    __device__ __forceinline__ void flush(unsigned long long *) {}
+};
+template <> struct Counters<true> {
+    unsigned long long v[K_COUNT];
+    __device__ Counters() { for (int i = 0; i < K_COUNT; i++) v[i] = 0; }
+    __device__ __forceinline__ void add(int k, uint32_t n) { v[k] += n; }
+    __device__ __forceinline__ void flops(uint32_t n) { v[K_FLOPS_WRITTEN] += n; v[K_FLOPS_MIN] += n; }
+    __device__ void flush(unsigned long long *g) {
+        for (int i = 0; i < K_COUNT; i++) {
+            unsigned long long s = v[i];
+            for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if ((threadIdx.x & 31) == 0 && s) atomicAdd(&g[i], s);
+        }
+    }
+};
+
+}  // namespace trt

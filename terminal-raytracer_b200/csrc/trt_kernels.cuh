@@ -1,0 +1,97 @@
+// trt_kernels.cuh -- __global__ entry points of the trace path (sm_100a).
+#pragma once
+#include "trt_trace.cuh"
+
+namespace trt {
+
+// ---- K0: scene repack, AoS 180 B (primitive.rs:4-34) -> SoA float4 arrays --------------------------
+// Derived values use the same helper functions (and therefore the same roundings, in the context's
+// arithmetic convention) as the shader expressions they replace:
+//   r*r (shader.wgsl:264), edge1/edge2 (:193-194,:240-241,:386-387), normalize(plane_normal) (:238),
+//   normalize(cross(edge1,edge2)) (:242,:388), 0.5*length(cross) (:389), 4*pi*r*r (:369).
+struct RepackParams {
+    const trt_primitive *aos;
+    int n_prims;
+    float4 *ga, *gb, *gc, *gn, *mc, *me;
+    const int *light_prim;       // prim index of each light (host-built, scan order)
+    int n_lights;
+    float4 *la, *lb, *lc, *ln, *le;
+};
+
+__device__ __forceinline__ float3 ld3(const trt_vec3 &v) { return make_float3(v.x, v.y, v.z); }
+__device__ __forceinline__ float4 f4(float3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
+
+template <int CONV>
+__global__ void repack_kernel(RepackParams rp) {
+    typedef M<CONV> V;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < rp.n_prims) {
+        const trt_primitive &p = rp.aos[i];
+        float4 a = make_float4(0, 0, 0, 0), b = a, c = a, n = make_float4(0.0f, 1.0f, 0.0f, 0.0f);
+        if (p.primitive_type == 0u) {
+            a = f4(ld3(p.sphere_center), p.sphere_radius);
+            b.x = p.sphere_radius * p.sphere_radius;
+        } else if (p.primitive_type == 1u) {
+            a = f4(ld3(p.plane_point), 0.0f);
+            b = f4(ld3(p.plane_normal), 0.0f);
+            n = f4(V::normalize(ld3(p.plane_normal)), 0.0f);
+        } else if (p.primitive_type == 2u) {
+            float3 e1 = V::sub(ld3(p.triangle_v1), ld3(p.triangle_v0));
+            float3 e2 = V::sub(ld3(p.triangle_v2), ld3(p.triangle_v0));
+            a = f4(ld3(p.triangle_v0), 0.0f);
+            b = f4(e1, 0.0f);
+            c = f4(e2, 0.0f);
+            n = f4(V::normalize(V::cross(e1, e2)), 0.0f);
+        }
+        rp.ga[i] = a; rp.gb[i] = b; rp.gc[i] = c; rp.gn[i] = n;
+        rp.mc[i] = f4(ld3(p.color), p.reflectivity);
+        rp.me[i] = f4(ld3(p.emission), __int_as_float((int)p.primitive_type));
+    }
+    if (i < rp.n_lights) {
+        const trt_primitive &p = rp.aos[rp.light_prim[i]];
+        float4 a, b = make_float4(0, 0, 0, 0), c = b, n;
+        if (p.primitive_type == 0u) {
+            a = f4(ld3(p.sphere_center), p.sphere_radius);
+            n = make_float4(0, 0, 0, TRT_FOUR_PI_F * p.sphere_radius * p.sphere_radius);
+        } else {
+            float3 e1 = V::sub(ld3(p.triangle_v1), ld3(p.triangle_v0));
+            float3 e2 = V::sub(ld3(p.triangle_v2), ld3(p.triangle_v0));
+            float3 cr = V::cross(e1, e2);
+            a = f4(ld3(p.triangle_v0), 0.0f);
+            b = f4(ld3(p.triangle_v1), 0.0f);
+            c = f4(ld3(p.triangle_v2), 0.0f);
+            n = f4(V::normalize(cr), 0.5f * V::length(cr));
+        }
+        rp.la[i] = a; rp.lb[i] = b; rp.lc[i] = c; rp.ln[i] = n;
+        rp.le[i] = f4(ld3(p.emission), __int_as_float((int)p.primitive_type));
+    }
+}
+
+// ---- K2 (v0): one thread per pixel, loops exactly as shader.wgsl main() ----------------------------
+// Kept as the plain device restatement (and the instrumented build); the production kernel is
+// trace_persistent_kernel below.
+template <int CONV, bool COUNT>
+__global__ void __launch_bounds__(128) trace_pixel_kernel(SceneView sc, LightView lv, FrameParams fp) {
+    Counters<COUNT> cn;
+    Tracer<CONV, COUNT> tr(sc, lv, fp, cn);
+    const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp < fp.n_local_pixels) {
+        const uint32_t lr = lp / fp.width, x = lp - lr * fp.width;
+        const uint32_t y = fp.row_map ? fp.row_map[lr] : lr;
+        tr.pixel(x, y);
+    }
+    if (COUNT) cn.flush(fp.counters);
+}
+
+// pack the rows this shard owns contiguously (local row order) for the NCCL gather
+__global__ void pack_rows_kernel(const float4 *src, float4 *dst, const uint32_t *row_map, uint32_t width,
+                                 uint32_t n_local_pixels) {
+    const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp < n_local_pixels) {
+        const uint32_t lr = lp / width, x = lp - lr * width;
+        const uint32_t y = row_map ? row_map[lr] : lr;
+        dst[lp] = src[(size_t)y * width + x];
+    }
+}
+
+}  // namespace trt

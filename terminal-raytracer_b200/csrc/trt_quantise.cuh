@@ -1,0 +1,192 @@
+// trt_quantise.cuh -- on-device terminal quantiser: float4 frame -> ANSI byte stream.
+//
+// Replaces the reference's CPU row formatter /root/reference/src/lib.rs:503-532 (rayon, one String
+// per row, concat).  Byte grammar per pixel (lib.rs:513,524):  ESC[38;2;R;G;Bm <glyph> ESC[0m,
+// glyph = U+2588 (E2 96 88) in truecolor mode or one of the 68 ramp characters in ASCII mode;
+// "\r\n" after each row (lib.rs:527).  Only the byte stream crosses PCIe.
+//
+// Three launches (HBM-bound; DESIGN.md "Quantiser"):
+//   quant_pack   : 16 B/px in  -> 4 B/px packed (R,G,B,glyph) + per-block byte counts
+//   quant_scan   : exclusive scan of the block counts (one CTA), total length
+//   quant_emit   : 4 B/px in -> bytes staged in shared memory -> 16-byte aligned coalesced stores
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace trt {
+
+#define TRT_Q_BLOCK 256            // pixels per CTA in pack/emit
+#define TRT_Q_STAGE (TRT_Q_BLOCK * 28 + 32)
+
+struct QuantParams {
+    const float4 *src;             // frame (float4 per pixel)
+    const uint64_t *row_src;       // per global row: element offset of its first pixel in src, or NULL (y*w)
+    uint32_t width, height;
+    int mode;                      // 0 ASCII, 1 truecolor
+    uint32_t *packed;              // n_pixels
+    uint32_t *block_len;           // n_blocks
+    uint64_t *block_off;           // n_blocks + 1 (last = total)
+    uint32_t n_blocks;
+    uint8_t *out;
+    uint64_t out_cap;
+};
+
+// lib.rs:521 -- 68 glyphs
+__constant__ char c_ramp[69] = " .`^\",:;Il!i><~+_-?][}{1)(|\\tfjrxnuvczXYUJCLQ0OZmwqpdbkhao*#MW&8%B@$";
+
+// Rust: (v).clamp(0.0, 255.0) as u8 -- clamp keeps NaN, `as u8` truncates, saturates, NaN -> 0
+__device__ __forceinline__ uint32_t to_u8(float v) {
+    if (!(v > 0.0f)) return 0u;
+    if (v >= 255.0f) return 255u;
+    return (uint32_t)v;
+}
+// Rust f32::powf(x, 0.3) = glibc powf on Linux.  Evaluated in double and rounded once: equals the
+// correctly rounded f32 power except on double-rounding ties (byte-level differences
+// against glibc powf are confined to quantisation-boundary pixels, counted by the tests).
+__device__ __forceinline__ float powf_03(float x) { return (float)pow((double)x, (double)0.3f); }
+
+__device__ __forceinline__ uint32_t quantise_pixel(float4 p, int mode) {
+    uint32_t r, g, b, ci = 0;
+    if (mode == 1) {                                    // lib.rs:510-512
+        r = to_u8(sqrtf(p.x) * 255.0f);
+        g = to_u8(sqrtf(p.y) * 255.0f);
+        b = to_u8(sqrtf(p.z) * 255.0f);
+    } else {                                            // lib.rs:515-523
+        r = to_u8(powf_03(p.x) * 255.0f);
+        g = to_u8(powf_03(p.y) * 255.0f);
+        b = to_u8(powf_03(p.z) * 255.0f);
+        float brightness = 0.2126f * p.x + 0.7152f * p.y + 0.0722f * p.z;
+        float c = powf_03(brightness) * 67.0f;
+        // f32::min(c, 67.0): NaN -> 67; then `as usize` (negative/NaN -> 0)
+        if (c != c || c > 67.0f) c = 67.0f;
+        ci = (c > 0.0f) ? (uint32_t)c : 0u;
+    }
+    return r | (g << 8) | (b << 16) | (ci << 24);
+}
+
+__device__ __forceinline__ uint32_t ndigits(uint32_t v) { return 1u + (v >= 10u) + (v >= 100u); }
+
+__device__ __forceinline__ uint32_t pixel_len(uint32_t pk, int mode, bool row_end) {
+    uint32_t n = 14u + ndigits(pk & 255u) + ndigits((pk >> 8) & 255u) + ndigits((pk >> 16) & 255u) + (mode == 1 ? 3u : 1u);
+    return n + (row_end ? 2u : 0u);
+}
+
+__device__ __forceinline__ uint32_t put_u8(uint8_t *dst, uint32_t v) {
+    uint32_t n = 0;
+    if (v >= 100u) { dst[n++] = (uint8_t)('0' + v / 100u); v %= 100u; dst[n++] = (uint8_t)('0' + v / 10u); v %= 10u; }
+    else if (v >= 10u) { dst[n++] = (uint8_t)('0' + v / 10u); v %= 10u; }
+    dst[n++] = (uint8_t)('0' + v);
+    return n;
+}
+
+__device__ __forceinline__ void put_pixel(uint8_t *d, uint32_t pk, int mode, bool row_end) {
+    d[0] = 0x1b; d[1] = '['; d[2] = '3'; d[3] = '8'; d[4] = ';'; d[5] = '2'; d[6] = ';';
+    uint32_t n = 7;
+    n += put_u8(d + n, pk & 255u); d[n++] = ';';
+    n += put_u8(d + n, (pk >> 8) & 255u); d[n++] = ';';
+    n += put_u8(d + n, (pk >> 16) & 255u); d[n++] = 'm';
+    if (mode == 1) { d[n++] = 0xE2; d[n++] = 0x96; d[n++] = 0x88; }
+    else d[n++] = (uint8_t)c_ramp[pk >> 24];
+    d[n++] = 0x1b; d[n++] = '['; d[n++] = '0'; d[n++] = 'm';
+    if (row_end) { d[n++] = '\r'; d[n++] = '\n'; }
+}
+
+// CTA-wide exclusive scan of one u32 per thread (TRT_Q_BLOCK threads); returns the CTA total
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t &total) {
+    __shared__ uint32_t warp_sums[TRT_Q_BLOCK / 32];
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    uint32_t inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= (uint32_t)o) inc += t;
+    }
+    if (lane == 31u) warp_sums[wid] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+    for (uint32_t w = 0; w < TRT_Q_BLOCK / 32; w++) {
+        uint32_t s = warp_sums[w];
+        if (w < wid) base += s;
+        tot += s;
+    }
+    total = tot;
+    __syncthreads();
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(TRT_Q_BLOCK) quant_pack_kernel(QuantParams q) {
+    const uint64_t n = (uint64_t)q.width * q.height;
+    const uint64_t i = (uint64_t)blockIdx.x * TRT_Q_BLOCK + threadIdx.x;
+    uint32_t len = 0;
+    if (i < n) {
+        const uint32_t y = (uint32_t)(i / q.width), x = (uint32_t)(i - (uint64_t)y * q.width);
+        const uint64_t s = q.row_src ? q.row_src[y] + x : i;
+        const uint32_t pk = quantise_pixel(__ldg(&q.src[s]), q.mode);
+        q.packed[i] = pk;
+        len = pixel_len(pk, q.mode, x == q.width - 1u);
+    }
+    uint32_t total;
+    block_exclusive_scan(len, total);
+    if (threadIdx.x == 0) q.block_len[blockIdx.x] = total;
+}
+
+// one CTA of 1024 threads: exclusive scan of n_blocks counts into 64-bit offsets
+__global__ void __launch_bounds__(1024) quant_scan_kernel(QuantParams q) {
+    __shared__ uint64_t warp_sums[32];
+    __shared__ uint64_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < q.n_blocks; base += 1024u) {
+        const uint32_t i = base + threadIdx.x;
+        const uint64_t v = (i < q.n_blocks) ? q.block_len[i] : 0ull;
+        uint64_t inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            uint64_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= (uint32_t)o) inc += t;
+        }
+        if (lane == 31u) warp_sums[wid] = inc;
+        __syncthreads();
+        uint64_t wbase = 0, tot = 0;
+        for (uint32_t w = 0; w < 32u; w++) {
+            uint64_t s = warp_sums[w];
+            if (w < wid) wbase += s;
+            tot += s;
+        }
+        const uint64_t carry = carry_s;
+        if (i < q.n_blocks) q.block_off[i] = carry + wbase + inc - v;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = carry + tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) q.block_off[q.n_blocks] = carry_s;
+}
+
+__global__ void __launch_bounds__(TRT_Q_BLOCK) quant_emit_kernel(QuantParams q) {
+    __shared__ __align__(16) uint8_t stage[TRT_Q_STAGE];
+    const uint64_t n = (uint64_t)q.width * q.height;
+    const uint64_t i = (uint64_t)blockIdx.x * TRT_Q_BLOCK + threadIdx.x;
+    const uint64_t off = q.block_off[blockIdx.x];
+    const uint32_t pad = (uint32_t)((uintptr_t)(q.out + off) & 15u);
+    uint32_t pk = 0, len = 0;
+    bool row_end = false;
+    if (i < n) {
+        pk = q.packed[i];
+        row_end = (uint32_t)(i % q.width) == q.width - 1u;
+        len = pixel_len(pk, q.mode, row_end);
+    }
+    uint32_t total;
+    const uint32_t local = block_exclusive_scan(len, total);
+    if (off + total > q.out_cap) return;                 // caller checks the length first
+    if (i < n) put_pixel(stage + pad + local, pk, q.mode, row_end);
+    __syncthreads();
+    uint8_t *dst = q.out + off;                          // dst + k  <->  stage[pad + k]
+    const uint32_t head = min(total, (16u - pad) & 15u); // bytes before the first 16-byte boundary
+    const uint32_t body = (total - head) & ~15u;
+    for (uint32_t k = threadIdx.x; k < head; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(stage + pad + head);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
+    for (uint32_t k = threadIdx.x; k < body / 16u; k += TRT_Q_BLOCK) d4[k] = s4[k];
+    for (uint32_t k = head + body + threadIdx.x; k < total; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
+}
+
+}  // namespace trt

@@ -1,0 +1,359 @@
+// trt_trace.cuh -- ray generation, linear-scan intersection, NEE, bounce, roulette: the per-ray
+// device functions shared by the trace kernels.  Follows /root/reference/src/shader.wgsl (cited).
+#pragma once
+#include "trt_device.cuh"
+
+namespace trt {
+
+struct LightView {               // emissive spheres / triangles in scan order (shader.wgsl:342-392)
+    const float4 *la, *lb, *lc;  // sphere: la = (c, r); triangle: la = v0, lb = v1, lc = v2
+    const float4 *ln;            // (light normal xyz [triangle], area)
+    const float4 *le;            // (emission rgb, type as float bits)
+};
+
+template <int CONV, bool COUNT>
+struct Tracer {
+    typedef M<CONV> V;
+    const SceneView &sc;
+    const LightView &lv;
+    const FrameParams &fp;
+    Counters<COUNT> &cn;
+
+    __device__ Tracer(const SceneView &s, const LightView &l, const FrameParams &f, Counters<COUNT> &c)
+        : sc(s), lv(l), fp(f), cn(c) {}
+
+    // ---- single-primitive tests; `closest` is the current upper bound (shader.wgsl:258-277) -------
+    // sphere: pre-reject shader.wgsl:260-269, then hit_sphere shader.wgsl:155-175 (oc == to_center,
+    // h == t_ca bit for bit, so they are computed once)
+    __device__ __forceinline__ float test_sphere(float3 ro, float3 rd, float4 a, float r2, float t_min, float closest,
+                                                 uint32_t &cost) const {
+        float3 tc = V::sub(xyz(a), ro);
+        float t_ca = V::dot(tc, rd);
+        float tcc = V::dot(tc, tc);
+        float dist2 = V::nmadd(tcc, t_ca, t_ca);
+        cost = 18;
+        if (dist2 > r2 || t_ca + a.w < t_min || t_ca - a.w > closest) return -1.0f;
+        float c = tcc - r2;
+        float disc = V::msub(t_ca, t_ca, c);
+        cost = 37;
+        if (disc < 0.0f) return -1.0f;
+        float sq = sqrtf(disc);
+        float root = t_ca - sq;
+        if (root <= t_min || closest <= root) {
+            cost = 38;
+            root = t_ca + sq;
+            if (root <= t_min || closest <= root) return -1.0f;
+        }
+        return root;
+    }
+    // shader.wgsl:178-189
+    __device__ __forceinline__ float test_plane(float3 ro, float3 rd, float4 p, float4 n, float t_min, float closest,
+                                                uint32_t &cost) const {
+        float denom = V::dot(xyz(n), rd);
+        cost = 5;
+        if (fabsf(denom) < 0.0001f) return -1.0f;
+        cost = 14;
+        float t = V::dot(V::sub(xyz(p), ro), xyz(n)) / denom;
+        if (t < t_min || t > closest) return -1.0f;
+        return t;
+    }
+    // shader.wgsl:192-223 with edge1/edge2 precomputed (same f32 subtraction)
+    __device__ __forceinline__ float test_triangle(float3 ro, float3 rd, float4 v0, float4 e1, float4 e2, float t_min,
+                                                   float closest, uint32_t &cost) const {
+        float3 h = V::cross(rd, xyz(e2));
+        float a = V::dot(xyz(e1), h);
+        cost = 20;
+        if (a > -0.00001f && a < 0.00001f) return -1.0f;
+        float f = 1.0f / a;
+        float3 s = V::sub(ro, xyz(v0));
+        float u = f * V::dot(s, h);
+        cost = 30;
+        if (u < 0.0f || u > 1.0f) return -1.0f;
+        float3 q = V::cross(s, xyz(e1));
+        float v = f * V::dot(rd, q);
+        cost = 46;
+        if (v < 0.0f || u + v > 1.0f) return -1.0f;
+        cost = 52;
+        float t = f * V::dot(xyz(e2), q);
+        if (t > t_min && t < closest) return t;
+        return -1.0f;
+    }
+
+    // ---- hit_scene as written (shader.wgsl:248-294): full scan, narrowing bound, first index wins
+    // ties.  The record is completed once from the final (t, index) -- same values as updating it on
+    // every improvement.  shadow_needed: -1 closest-hit scan; 0/1 shadow scan (counting only).
+    __device__ __forceinline__ float scan_closest(float3 ro, float3 rd, float t_min, float t_max, int &best,
+                                                  int shadow_needed) {
+        float closest = t_max;
+        best = -1;
+        bool found = false;
+        for (int r = 0; r < sc.n_runs; r++) {
+            int4 run = __ldg(&sc.runs[r]);
+            for (int i = run.y; i < run.z; i++) {
+                float t = -1.0f;
+                uint32_t cost = 0;
+                if (run.x == 0) {
+                    t = test_sphere(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]).x, t_min, closest, cost);
+                } else if (run.x == 1) {
+                    t = test_plane(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), t_min, closest, cost);
+                } else if (run.x == 2) {
+                    t = test_triangle(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), __ldg(&sc.gc[i]), t_min, closest, cost);
+                }
+                if (COUNT) {
+                    cn.add(K_PRIM_TESTS, 1);
+                    cn.add(K_FLOPS_WRITTEN, cost);
+                    if (shadow_needed < 0 || (shadow_needed == 1 && !found)) {
+                        cn.add(K_PRIM_TESTS_MIN, 1);
+                        cn.add(K_FLOPS_MIN, cost);
+                    }
+                }
+                if (t > 0.0f && t < closest) {
+                    closest = t;
+                    best = i;
+                    if (COUNT) {
+                        // improving-hit cost needs the facing of this candidate
+                        float3 p = V::axpy(ro, rd, t);
+                        float3 n = normal_at(i, run.x, p);
+                        bool front = V::dot(rd, n) < 0.0f;
+                        uint32_t hc = 6u + (run.x == 0 ? 15u : run.x == 1 ? 9u : 24u) + 5u + (front ? 0u : 3u);
+                        cn.add(K_FLOPS_WRITTEN, hc);
+                        if (shadow_needed < 0) cn.add(K_FLOPS_MIN, hc);
+                        found = true;
+                    }
+                }
+            }
+        }
+        return best >= 0 ? closest : -1.0f;
+    }
+
+    // any-hit form of the same scan for shadow rays: only `hit.t < 0` is read by the caller
+    // (shader.wgsl:400-402), and before the first accepted hit the bound is still t_max, so stopping at
+    // the first accepted primitive returns the same truth value.
+    __device__ __forceinline__ bool scan_any(float3 ro, float3 rd, float t_min, float t_max) {
+        uint32_t cost;
+        for (int r = 0; r < sc.n_runs; r++) {
+            int4 run = __ldg(&sc.runs[r]);
+            for (int i = run.y; i < run.z; i++) {
+                float t = -1.0f;
+                if (run.x == 0) t = test_sphere(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]).x, t_min, t_max, cost);
+                else if (run.x == 1) t = test_plane(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), t_min, t_max, cost);
+                else if (run.x == 2) t = test_triangle(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), __ldg(&sc.gc[i]), t_min, t_max, cost);
+                if (t > 0.0f && t < t_max) return true;
+            }
+        }
+        return false;
+    }
+
+    // shader.wgsl:234-245 (plane / triangle normals precomputed with the same operations)
+    __device__ __forceinline__ float3 normal_at(int i, int type, float3 p) const {
+        if (type == 0) {
+            float4 a = __ldg(&sc.ga[i]);
+            return V::normalize(V::divs(V::sub(p, xyz(a)), a.w));
+        }
+        if (type == 1 || type == 2) return xyz(__ldg(&sc.gn[i]));
+        return f3(0.0f, 1.0f, 0.0f);
+    }
+
+    // shader.wgsl:297-304
+    __device__ __forceinline__ float3 sky(float3 d) const {
+        float t = 0.5f * (d.y + 1.0f);
+        float3 c = V::add(V::scale(f3(1.0f, 1.0f, 1.0f), 1.0f - t), V::scale(f3(0.5f, 0.7f, 1.0f), t));
+        return V::scale(c, 0.8f);
+    }
+
+    // shader.wgsl:312-335
+    __device__ __forceinline__ float3 cosine_hemisphere(uint32_t &rng, float3 normal) {
+        float r1 = rnd(rng), r2 = rnd(rng);
+        if (COUNT) cn.add(K_RNG_DRAWS, 2);
+        float cos_theta = sqrtf(r1);
+        float sin_theta = sqrtf(1.0f - r1);
+        float phi = TRT_TWO_PI_F * r2;
+        float sp, cp;
+        sincos_pinned(phi, sp, cp);
+        float x = sin_theta * cp, y = sin_theta * sp, z = cos_theta;
+        float3 w = V::normalize(normal);
+        float3 u = (fabsf(w.x) > 0.1f) ? V::normalize(V::cross(f3(0.0f, 1.0f, 0.0f), w))
+                                       : V::normalize(V::cross(f3(1.0f, 0.0f, 0.0f), w));
+        float3 v = V::cross(w, u);
+        return V::normalize(V::lin3(u, x, v, y, w, z));
+    }
+
+    // shader.wgsl:338-436.  The loop runs over the precomputed list of emissive spheres/triangles
+    // (same order; plane emitters and dark primitives consume no random numbers, :346-347,:390-392).
+    __device__ __forceinline__ float3 direct_lighting(uint32_t &rng, float3 hit_point, float3 normal, float3 color,
+                                                      float3 attenuation) {
+        float3 direct = f3(0.0f, 0.0f, 0.0f);
+        for (int k = 0; k < sc.n_lights; k++) {
+            float4 a = __ldg(&lv.la[k]);
+            float4 nl = __ldg(&lv.ln[k]);
+            float4 em = __ldg(&lv.le[k]);
+            int type = __float_as_int(em.w);
+            float3 light_point, light_normal;
+            float r1 = rnd(rng), r2 = rnd(rng);
+            if (COUNT) cn.add(K_RNG_DRAWS, 2);
+            if (type == 0) {                                   // uniform sphere sampling :352-369
+                float cos_theta = 1.0f - 2.0f * r1;
+                float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+                float phi = TRT_TWO_PI_F * r2;
+                float sp, cp;
+                sincos_pinned(phi, sp, cp);
+                float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
+                light_point = V::axpy(xyz(a), local, a.w);
+                light_normal = local;
+                if (COUNT) cn.flops(20);
+            } else {                                           // uniform triangle sampling :370-389
+                float sqrt_r1 = sqrtf(r1);
+                float u = 1.0f - sqrt_r1;
+                float v = r2 * sqrt_r1;
+                light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(__ldg(&lv.lb[k])), u, xyz(__ldg(&lv.lc[k])), v);
+                light_normal = xyz(nl);
+                if (COUNT) cn.flops(60);
+            }
+            float light_area = nl.w;
+            float3 light_vec = V::sub(light_point, hit_point);
+            float light_distance = V::length(light_vec);
+            float3 light_dir = V::divs(light_vec, light_distance);
+            float3 so = V::axpy(hit_point, normal, 0.001f);
+            if (COUNT) cn.flops(19);
+            // the two cosines do not depend on the shadow test (:403-404), so they are evaluated first
+            float cos_surface = fmaxf(0.0f, V::dot(normal, light_dir));
+            float cos_light = fmaxf(0.0f, V::dot(light_normal, V::scale(light_dir, -1.0f)));
+            bool needed = cos_surface > 0.0f && cos_light > 0.0f;
+            bool unoccluded;
+            if (COUNT) {
+                cn.add(K_SHADOW_SCANS, 1);
+                cn.add(K_SHADOW_NEEDED, needed ? 1u : 0u);
+                int dummy;
+                unoccluded = scan_closest(so, light_dir, 0.001f, light_distance - 0.001f, dummy, needed ? 1 : 0) < 0.0f;
+                if (unoccluded) { cn.add(K_SHADOW_UNOCCLUDED, 1); cn.flops(13); }
+            } else {
+                // a scan whose result cannot change the sum is skipped (no RNG inside hit_scene)
+                unoccluded = needed && !scan_any(so, light_dir, 0.001f, light_distance - 0.001f);
+            }
+            if (unoccluded && needed) {
+                if (COUNT) { cn.add(K_SHADOW_LIT, 1); cn.flops(19); }
+                float distance_squared = light_distance * light_distance;
+                float geometric = (cos_surface * cos_light) / distance_squared;
+                float3 brdf = V::divs(color, TRT_PI_F);
+                float3 contrib = V::mulv(V::mulv(brdf, xyz(em)), V::scale(attenuation, geometric * light_area));
+                direct = V::add(direct, f3(fminf(contrib.x, 10.0f), fminf(contrib.y, 10.0f), fminf(contrib.z, 10.0f)));
+            }
+        }
+        return direct;
+    }
+
+    // shader.wgsl:439-495
+    __device__ __forceinline__ float3 ray_color(uint32_t &rng, float3 ro, float3 rd) {
+        float3 acc = f3(0.0f, 0.0f, 0.0f);
+        float3 att = f3(1.0f, 1.0f, 1.0f);
+        for (uint32_t i = 0; i < fp.max_depth; i++) {
+            int idx;
+            if (COUNT) cn.add(K_CLOSEST_SCANS, 1);
+            float t = scan_closest(ro, rd, 0.001f, 1e10f, idx, -1);
+            if (t < 0.0f) {
+                if (COUNT) { cn.add(K_MISSES, 1); cn.flops(21); }
+                acc = V::vmad(acc, sky(rd), att);
+                break;
+            }
+            if (COUNT) { cn.add(K_HITS, 1); cn.flops(9); }
+            float4 mc = __ldg(&sc.mc[idx]);
+            float4 me = __ldg(&sc.me[idx]);
+            int type = __float_as_int(me.w);
+            float3 p = V::axpy(ro, rd, t);
+            float3 n = normal_at(idx, type, p);
+            if (!(V::dot(rd, n) < 0.0f)) n = V::scale(n, -1.0f);
+            acc = V::vmad(acc, xyz(me), att);
+            acc = V::add(acc, direct_lighting(rng, p, n, xyz(mc), att));
+            float3 scatter;
+            if (COUNT) cn.add(K_RNG_DRAWS, 1);
+            if (mc.w > rnd(rng)) {
+                if (COUNT) { cn.add(K_MIRROR, 1); cn.flops(12); }
+                scatter = V::reflect(rd, n);
+            } else {
+                if (COUNT) { cn.add(K_DIFFUSE, 1); cn.flops(75); }
+                scatter = cosine_hemisphere(rng, n);
+            }
+            att = V::mulv(att, xyz(mc));
+            if (COUNT) cn.flops(9);
+            ro = V::axpy(p, scatter, 0.001f);
+            rd = scatter;
+            if (i > 3u) {
+                float survival = fminf(0.95f, fmaxf(att.x, fmaxf(att.y, att.z)));
+                if (COUNT) { cn.add(K_ROULETTE_TESTS, 1); cn.add(K_RNG_DRAWS, 1); }
+                if (survival < rnd(rng)) { if (COUNT) cn.add(K_ROULETTE_KILLS, 1); break; }
+                if (COUNT) cn.flops(3);
+                att = V::divs(att, survival);
+            }
+        }
+        return acc;
+    }
+
+    // shader.wgsl:519-546
+    __device__ __forceinline__ void camera_ray(uint32_t &rng, uint32_t x, uint32_t y, float3 &ro, float3 &rd) {
+        if (COUNT) cn.add(K_RNG_DRAWS, 2);
+        float u = (__uint2float_rn(x) + rnd(rng)) / fp.wm1;
+        float v = (__uint2float_rn(fp.height - 1u - y) + rnd(rng)) / fp.hm1;
+        float ndc_x = 2.0f * u - 1.0f;
+        float ndc_y = (2.0f * v - 1.0f) / fp.char_aspect;
+        float vx = fp.half_w * ndc_x;
+        float vy = fp.half_h * ndc_y;
+        rd = V::normalize(V::lin3(fp.cam_right, vx, fp.cam_up, vy, fp.cam_fwd, 1.0f));
+        ro = fp.cam_pos;
+    }
+
+    // shader.wgsl:499-621 for one pixel
+    __device__ __forceinline__ void pixel(uint32_t x, uint32_t y) {
+        uint32_t rng = (y * fp.width + x) * 1973u + fp.seed * 9277u + fp.frame_number * 12345u;
+        float3 pixel_color = f3(0, 0, 0), color_sum = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
+        const uint32_t base = fp.base_samples, max_samples = fp.spp;
+        if (COUNT) { cn.add(K_PIXELS, 1); cn.flops(30); }
+        for (uint32_t i = 0; i < base; i++) {
+            rng = pcg_hash(rng + i * 5096u);
+            float3 ro, rd;
+            camera_ray(rng, x, y, ro, rd);
+            float3 c = ray_color(rng, ro, rd);
+            pixel_color = V::add(pixel_color, c);
+            color_sum = V::add(color_sum, c);
+            sq_sum = V::add(sq_sum, V::mulv(c, c));
+            if (COUNT) { cn.add(K_SAMPLES_BASE, 1); cn.flops(50); }
+        }
+        float3 mean = V::divs(color_sum, fp.base_f);
+        float3 var_vec = V::sub(V::divs(sq_sum, fp.base_f), V::mulv(mean, mean));
+        float variance_value = var_vec.x + var_vec.y + var_vec.z;
+        if (variance_value > 10.0f && base < max_samples) {
+            uint32_t additional = min(max_samples - base, __float2uint_rz(variance_value * 50.0f));
+            for (uint32_t i = 0; i < additional; i++) {
+                rng = pcg_hash(rng + (base + i) * 5096u);
+                float3 ro, rd;
+                camera_ray(rng, x, y, ro, rd);
+                pixel_color = V::add(pixel_color, ray_color(rng, ro, rd));
+                if (COUNT) { cn.add(K_SAMPLES_EXTRA, 1); cn.flops(41); }
+            }
+            pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(base + additional));
+        }
+        finish_pixel(x, y, pixel_color, variance_value);
+    }
+
+    // shader.wgsl:605-621: variance store, temporal accumulation, pixel store (float4, coalesced)
+    __device__ __forceinline__ void finish_pixel(uint32_t x, uint32_t y, float3 pixel_color, float variance_value) {
+        size_t index = (size_t)y * fp.width + x;
+        trt_variance vb;
+        vb.variance = variance_value;
+        vb.sample_count = fp.base_samples;
+        fp.variance[index] = vb;
+        float3 cur = V::divs(pixel_color, fp.spp_f);
+        float4 out;
+        if (fp.frame_number == 0u) {
+            out = make_float4(cur.x, cur.y, cur.z, 0.0f);
+        } else {
+            float alpha = 1.0f / __uint2float_rn(fp.frame_number + 1u);
+            float4 a = fp.accumulation[index];
+            float3 r = V::add(V::scale(xyz(a), 1.0f - alpha), V::scale(cur, alpha));
+            out = make_float4(r.x, r.y, r.z, 0.0f);
+        }
+        fp.accumulation[index] = out;
+        fp.pixels[index] = out;
+    }
+};
+
+}  // namespace trt
