@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""
+bench.py -- Msamples/s (path samples per second) of the per-pixel path-tracing hot path on B200.
+
+  python bench.py --gpus N --steps K --warmup W                 (our arm; torchrun for N > 1)
+  python bench.py --impl reference --gpus N --steps K --warmup W (reference arm: CPU restatement)
+
+A "step" is one frame of the workload through the hot path.  Default workload = BASELINE.json
+configs[2] "c3": Cornell box 3840x2160, 1024 spp, max_depth 32, truecolor stream, rows sharded over
+the N GPUs (the configuration the metric "Cornell Box at 1/2/4/8 B200" is quoted on; total work is
+fixed as N grows => "scaling": "strong").  --workload c1|c2|c4 select the other configs.
+
+`value`  : device-resident (scene + buffers in HBM; trace + accumulate + gather + quantise).
+`e2e`    : the same through trt_render_frame with HOST buffers: uniforms in, byte stream out (pinned).
+`roofline`: trace kernel, FP32: achieved = F_min (algorithmic flops) / CUDA-event time.
+`cpu_baseline`: the oracle (C restatement of the shader; the reference has no CPU tracer) on a bounded
+            strided pixel sample of the same frame, all host threads.
+Only the cpu_baseline / --impl reference legs touch oracle/.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as graft  # noqa: E402
+
+NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # 74.45: SMs x lanes x 2 x max clock
+
+
+def workload(name, O, args):
+    """-> dict(scene, width, height, spp, depth, mode, frames_accumulate, seed_fn, label)"""
+    if name in ("c1", "c2", "c3"):
+        sc = O.CORNELL
+        if name == "c1":
+            w, h, spp, mode, acc = 400, 200, 16, 0, False
+        elif name == "c2":
+            w, h, spp, mode, acc = 400, 200, 16, 1, True
+        else:
+            w, h, spp, mode, acc = 3840, 2160, 1024, 1, False
+        depth = 32
+        seed_fn = (lambda f: O.c2_seed(f)) if acc else (lambda f: O.C1_SEED)
+        label = {"c1": "C1 Cornell_Box 400x200 16spp depth32 ASCII single frame",
+                 "c2": "C2 Cornell_Box 400x200 16spp depth32 truecolor, temporal accumulation (frame_number = step)",
+                 "c3": "C3 Cornell_Box 3840x2160 1024spp depth32 truecolor, rows sharded over the GPUs"}[name]
+    elif name == "c4":
+        sc = O.make_c4_scene()
+        w, h, spp, depth, mode, acc = 1920, 1080, 256, 32, 0, False
+        seed_fn = lambda f: O.C4_SEED  # noqa: E731
+        label = "C4 synthetic 4096 spheres + 16384 triangles + 2 emissive quads 1920x1080 256spp (linear scan)"
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    if args.width:
+        w = args.width
+    if args.height:
+        h = args.height
+    if args.spp:
+        spp = args.spp
+    if args.width or args.height or args.spp:
+        label += f" [OVERRIDE {w}x{h} {spp}spp: not the named config]"
+    return dict(scene=sc, w=w, h=h, spp=spp, depth=depth, mode=mode, acc=acc, seed_fn=seed_fn, label=label, name=name)
+
+
+def sample_indices(w, h, n):
+    """n pixel indices on a regular stride over the frame (deterministic)."""
+    total = w * h
+    n = max(1, min(n, total))
+    return np.unique((np.arange(n, dtype=np.float64) * (total / n)).astype(np.uint32))
+
+
+def cpu_run(O, wl, prims, n_pixels, threads, frame=0):
+    idx = sample_indices(wl["w"], wl["h"], n_pixels)
+    u = O.make_uniforms(wl["scene"], len(prims), wl["seed_fn"](frame), 0, width=wl["w"], height=wl["h"], spp=wl["spp"],
+                        max_depth=wl["depth"])
+    t0 = time.perf_counter()
+    r = O.render(prims, u, idx=idx, threads=threads)
+    dt = time.perf_counter() - t0
+    return r["samples_traced"], dt, len(idx)
+
+
+def cpu_sample_size(O, wl, prims, threads, budget_s):
+    """pick a pixel count worth ~budget_s seconds of CPU work from a short probe"""
+    O.render(prims, O.make_uniforms(wl["scene"], len(prims), 1, 0, width=32, height=16, spp=4, max_depth=4))   # spin up
+    probe = max(64, min(4096, wl["w"] * wl["h"] // 64))
+    s, dt, n = cpu_run(O, wl, prims, probe, threads)
+    while dt < 0.3 and probe < wl["w"] * wl["h"]:
+        probe = min(wl["w"] * wl["h"], probe * 4)
+        s, dt, n = cpu_run(O, wl, prims, probe, threads)
+    return int(max(64, min(wl["w"] * wl["h"], n * budget_s / max(dt, 1e-6))))
+
+
+def reference_arm(args):
+    """The reference's own implementation of the path is a WGSL shader behind wgpu (needs a graphics
+    adapter: unavailable on this box) and there is no CPU tracer in it; the reference arm is therefore
+    the oracle's CPU restatement on all host threads, on a bounded strided sample of the same frame."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    O = graft.load_oracle()
+    wl = workload(args.workload, O, args)
+    prims = O.flatten_scene(wl["scene"])
+    threads = O.max_threads()
+    budget = 60.0 / max(1, args.steps + args.warmup)
+    n_px = cpu_sample_size(O, wl, prims, threads, min(20.0, max(2.0, budget)))
+    for _ in range(args.warmup):
+        cpu_run(O, wl, prims, n_px, threads)
+    samples, secs = 0, 0.0
+    for k in range(args.steps):
+        s, dt, n = cpu_run(O, wl, prims, n_px, threads, frame=k if wl["acc"] else 0)
+        samples += s
+        secs += dt
+    val = samples / secs / 1e6
+    sample = f"{n} of {wl['w'] * wl['h']} pixels on a regular stride, every sample and bounce of those pixels"
+    line = {"impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["label"], "l2": "n/a (CPU)"},
+            "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "200",
+                                       "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out, _ = self.p.communicate()
+        sm, mx, reasons, power = [], [], set(), []
+        for ln in out.splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "power_w_max": max(power), "samples": len(sm)}
+
+
+def ours(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+        args.gpus = world
+    pkg = graft.load_package()
+    pkg.api.lib()                                     # fails loudly if the CUDA library is missing
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from terminal_raytracer_b200 import multigpu
+
+    O = graft.load_oracle() if rank == 0 else None    # scene data + uniforms restatement; cpu_baseline leg
+    OO = O or graft.load_oracle()                      # (scene constants only on other ranks)
+    wl = workload(args.workload, OO, args)
+    prims = OO.flatten_scene(wl["scene"])
+    w, h, mode = wl["w"], wl["h"], wl["mode"]
+
+    def uniforms(f):
+        u = OO.make_uniforms(wl["scene"], len(prims), wl["seed_fn"](f), f if wl["acc"] else 0, width=w, height=h,
+                             spp=wl["spp"], max_depth=wl["depth"])
+        return pkg.api.uniforms_from_bytes(u.tobytes())
+
+    sr = multigpu.ShardedRenderer(pkg, w, h, rank, world, stripe_rows=args.stripe_rows, device=local, conv=args.conv)
+    sr.upload_scene(prims)
+    stream = sr.stream
+    frame_bytes = w * h * 16
+    small = frame_bytes * 3 < 126 * 2**20
+    flush = torch.empty(256 * 2**20, dtype=torch.uint8, device=f"cuda:{local}") if small else None
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ------------------------------------------------------------------
+    for k in range(args.warmup):
+        sr.step(uniforms(k), mode)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    trace_ms, samples_local, launches = [], 0, 0
+    barrier()
+    for k in range(args.steps):
+        if flush is not None:
+            with torch.cuda.stream(stream):
+                flush.fill_(k & 0xFF)
+        evs[k][0].record(stream)
+        sr.step(uniforms(args.warmup + k), mode)
+        evs[k][1].record(stream)
+        # per-step statistics are read back after the step's stop event (they sync the stream)
+        t = sr.r.timings()
+        trace_ms.append(t.trace_ms)
+        launches += t.kernel_launches                 # trace + pack_rows + 3 quantise kernels (rank 0)
+        samples_local += sr.r.frame_stats().samples_traced
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    tt = torch.tensor([dev_ms, float(samples_local), float(sum(trace_ms))], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        mx = tt.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        dev_ms, samples_total, trace_sum_max = mx[0].item(), sm[1].item(), mx[2].item()
+    else:
+        samples_total, trace_sum_max = float(samples_local), float(sum(trace_ms))
+
+    # ---- end to end through trt_render_frame with host buffers (rank-local frame; N = 1 only is exact) ---
+    e2e = None
+    if world == 1:
+        r1 = sr.r
+        cap = w * h * 26 + 2 * h + 64
+        host = pkg.api._P()
+        assert pkg.api.lib().trt_alloc_host(cap, __import__("ctypes").byref(host)) == 0
+        for k in range(max(1, args.warmup // 2)):
+            r1.render_frame_into(uniforms(k), mode, host, cap)
+        torch.cuda.synchronize()
+        t_e2e, s_e2e, out_bytes = 0.0, 0, 0
+        for k in range(args.steps):
+            if flush is not None:
+                flush.fill_(k & 0xFF)
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            n = r1.render_frame_into(uniforms(args.warmup + k), mode, host, cap)    # blocks until bytes are on the host
+            t_e2e += time.perf_counter() - t0
+            s_e2e += r1.frame_stats().samples_traced
+            out_bytes += n
+        pkg.api.lib().trt_free_host(host)
+        e2e = {"value": s_e2e / t_e2e / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 160,
+               "d2h_bytes_per_step": out_bytes // args.steps + 8, "ms_per_step": t_e2e / args.steps * 1e3}
+    else:
+        # N > 1: the gathered frame is quantised on rank 0 and its byte stream read back to host memory
+        barrier()
+        t0 = time.perf_counter()
+        out_bytes = 0
+        for k in range(args.steps):
+            sr.step(uniforms(args.warmup + k), mode)
+            if rank == 0:
+                out_bytes += len(sr.r.read_stream())
+            barrier()
+        t_e2e = time.perf_counter() - t0
+        e2e = {"value": samples_total / t_e2e / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 160 * world,
+               "d2h_bytes_per_step": out_bytes // args.steps + 8, "ms_per_step": t_e2e / args.steps * 1e3}
+
+    if rank != 0:
+        sr.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the trace kernel: F_min per sample from the instrumented kernel on a row subset ----
+    sub = 1 if w * h * wl["spp"] <= 2_000_000 else max(1, args.count_stride)
+    rc = pkg.Renderer(w, h, device=local, conv=args.conv, count_work=True, shard_index=0, shard_count=sub, stripe_rows=1)
+    rc.upload_scene(prims)
+    rc.render_frame(uniforms(args.warmup), pkg.MODE_NONE)
+    cnt = rc.counters()
+    rc.close()
+    n_cnt = cnt["samples_base"] + cnt["samples_extra"]
+    fmin_per_sample = cnt["flops_min"] / max(1, n_cnt)
+    fwritten_per_sample = cnt["flops_written"] / max(1, n_cnt)
+    trace_s = trace_sum_max / 1e3
+    achieved = fmin_per_sample * samples_total / world / trace_s / 1e12 if trace_s > 0 else 0.0   # per GPU
+    ffma, sms, khz = pkg.api.measure_fp32_peak(local)
+    roofline = {"bound": "fp32", "kernel": "trace (persistent)" , "achieved": achieved, "peak": NOMINAL_FP32_TFLOPS,
+                "unit": "TFLOP/s", "frac": achieved / NOMINAL_FP32_TFLOPS, "traffic": None,
+                "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json holds no FP32 figure)",
+                "measured_ffma_tflops": ffma, "frac_of_measured_ffma": achieved / ffma if ffma else None,
+                "flops_min_per_sample": fmin_per_sample, "flops_written_per_sample": fwritten_per_sample,
+                "flops_basis": f"instrumented kernel on rows y % {sub} == 0 ({n_cnt} samples), DESIGN.md cost table",
+                "trace_ms_per_step": trace_s * 1e3 / args.steps, "per_gpu": True}
+
+    # ---- CPU baseline (oracle port, bounded sample) -----------------------------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        threads = O.max_threads()
+        n_px = cpu_sample_size(O, wl, prims, threads, args.cpu_seconds)
+        s, dt, n = cpu_run(O, wl, prims, n_px, threads)
+        cpu = {"value": s / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": "port",
+               "sample": f"{n} of {w * h} pixels on a regular stride ({s} samples, {dt:.1f} s)"}
+
+    value = samples_total / (dev_ms / 1e3) / 1e6
+    line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["label"], "samples_traced_per_step": samples_total / args.steps,
+                       "samples_nominal_per_step": w * h * wl["spp"], "conv": args.conv, "stripe_rows": args.stripe_rows,
+                       "l2": "256 MiB flush between timed steps" if small else "frame buffers (3 x %d MB) exceed the 126 MB L2" % (frame_bytes >> 20),
+                       "parallelism": f"rows x{world}"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    sr.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c4"])
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--spp", type=int, default=0)
+    ap.add_argument("--conv", type=int, default=0, choices=[0, 1])
+    ap.add_argument("--stripe-rows", type=int, default=4)
+    ap.add_argument("--count-stride", type=int, default=24, help="instrumented kernel runs on every n-th row")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -117,6 +117,14 @@ typedef struct trt_timings {
     uint32_t _pad;
 } trt_timings;
 
+/* always-on statistics of the last traced frame (this shard's rows) */
+typedef struct trt_frame_stats {
+    uint64_t samples_traced;      /* ray_color calls: sum over pixels of base + adaptive extra samples */
+    uint64_t bounces;             /* closest-hit scans (shader.wgsl:445) */
+    uint64_t pixels;
+    uint64_t reserved;
+} trt_frame_stats;
+
 /* replaces Instance/adapter/device + buffer creation, lib.rs:248-319 */
 int trt_create(const trt_config *cfg, trt_ctx **out);
 void trt_destroy(trt_ctx *ctx);
@@ -149,6 +157,10 @@ int trt_read_variance(trt_ctx *ctx, trt_variance *dst, size_t n_pixels);
 int trt_write_accumulation(trt_ctx *ctx, const float *src4, size_t n_pixels);
 int trt_get_counters(trt_ctx *ctx, trt_counters *out);
 int trt_get_timings(trt_ctx *ctx, trt_timings *out);
+int trt_get_frame_stats(trt_ctx *ctx, trt_frame_stats *out);
+/* register-resident FFMA loop on every SM: the measured FP32 FMA peak of this GPU in TFLOP/s
+ * (roofline denominator cross-check; nominal = SMs x 128 lanes x 2 x clock) */
+int trt_measure_fp32_peak(int device, float *tflops, int *sm_count, int *clock_khz);
 
 /* multi-GPU plumbing: raw device pointers of this context's buffers so that the host driver can
  * hand them to NCCL (gather of the shards' pixel rows), and a quantise that reads a caller-owned

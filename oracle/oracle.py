@@ -96,7 +96,7 @@ def lib() -> C.CDLL:
         L.oracle_render.restype = C.c_int
         L.oracle_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_uint32,
                                     C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
-                                    C.c_void_p, C.c_void_p]
+                                    C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]
         L.oracle_quantise.restype = C.c_size_t
         L.oracle_quantise.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_void_p,
                                       C.c_size_t, C.c_void_p]
@@ -266,15 +266,16 @@ def render(prims: np.ndarray, u: np.ndarray, accumulation: np.ndarray | None = N
     var = np.zeros(n, VARIANCE)
     cnt = np.zeros((), COUNTERS) if want_counters else None
     y0, y1 = rows if rows is not None else (0, h)
+    traced = C.c_uint64(0)
     if idx is not None:
         idx = np.ascontiguousarray(idx, np.uint32)
     rc = lib().oracle_render(prims.ctypes.data, ub.ctypes.data, conv, math_mode, threads, y0, y1,
                              idx.ctypes.data if idx is not None else None, n if idx is not None else 0,
                              accumulation.ctypes.data, pixels.ctypes.data, var.ctypes.data,
-                             cnt.ctypes.data if cnt is not None else None)
+                             cnt.ctypes.data if cnt is not None else None, C.byref(traced))
     if rc != 0:
         raise ValueError("oracle_render: bad arguments")
-    out = {"accumulation": accumulation, "pixels": pixels, "variance": var}
+    out = {"accumulation": accumulation, "pixels": pixels, "variance": var, "samples_traced": int(traced.value)}
     if cnt is not None:
         out["counters"] = {k: int(cnt[k]) for k in COUNTER_FIELDS}
     return out

@@ -182,11 +182,13 @@ static void counters_add(ocounters *dst, const ocounters *src) {
     for (size_t i = 0; i < sizeof(ocounters) / sizeof(uint64_t); i++) d[i] += s[i];
 }
 
-typedef void (*pixel_fn)(const ctx_t *, ocounters *, uint32_t, uint32_t, float *, float *, ovariance *);
+typedef uint32_t (*pixel_fn)(const ctx_t *, ocounters *, uint32_t, uint32_t, float *, float *, ovariance *);
 
 int oracle_render(const oprim *prims, const ouniforms *u, int conv, int math_mode, int threads,
                   uint32_t y0, uint32_t y1, const uint32_t *idx, uint64_t n_idx,
-                  float *accumulation, float *pixels, ovariance *variance, ocounters *counters) {
+                  float *accumulation, float *pixels, ovariance *variance, ocounters *counters,
+                  uint64_t *samples_traced) {
+    uint64_t traced_total = 0;
     if (!prims || !u || !accumulation || u->width == 0 || u->height == 0) return -1;
     if (conv != 0 && conv != 1) return -1;
     ctx_t cx = { prims, u, tanf(u->fov_rad / 2.0f), math_mode };
@@ -204,17 +206,19 @@ int oracle_render(const oprim *prims, const ouniforms *u, int conv, int math_mod
 #pragma omp parallel num_threads(nt)
         {
             ocounters local;
+            uint64_t traced = 0;
             memset(&local, 0, sizeof local);
 #pragma omp for schedule(dynamic, 16)
             for (int64_t k = 0; k < (int64_t)n_idx; k++) {
                 uint32_t gi = idx[k];
-                fn(&cx, &local, gi % w, gi / w, accumulation + 4 * k, pixels ? pixels + 4 * k : NULL,
-                   variance ? variance + k : NULL);
+                traced += fn(&cx, &local, gi % w, gi / w, accumulation + 4 * k, pixels ? pixels + 4 * k : NULL,
+                             variance ? variance + k : NULL);
             }
 #pragma omp critical
-            counters_add(&total, &local);
+            { counters_add(&total, &local); traced_total += traced; }
         }
         if (counters) counters_add(counters, &total);
+        if (samples_traced) *samples_traced = traced_total;
         return 0;
     }
     if (y1 > u->height) y1 = u->height;
@@ -226,18 +230,20 @@ int oracle_render(const oprim *prims, const ouniforms *u, int conv, int math_mod
 #pragma omp parallel num_threads(nt)
     {
         ocounters local;
+        uint64_t traced = 0;
         memset(&local, 0, sizeof local);
 #pragma omp for schedule(dynamic, 1)
         for (int64_t y = y0; y < (int64_t)y1; y++) {
             for (uint32_t x = 0; x < w; x++) {
                 size_t k = (size_t)y * w + x;
-                fn(&cx, &local, x, (uint32_t)y, accumulation + 4 * k, pixels ? pixels + 4 * k : NULL,
-                   variance ? variance + k : NULL);
+                traced += fn(&cx, &local, x, (uint32_t)y, accumulation + 4 * k, pixels ? pixels + 4 * k : NULL,
+                             variance ? variance + k : NULL);
             }
         }
 #pragma omp critical
-        counters_add(&total, &local);
+        { counters_add(&total, &local); traced_total += traced; }
     }
     if (counters) counters_add(counters, &total);
+    if (samples_traced) *samples_traced = traced_total;
     return 0;
 }

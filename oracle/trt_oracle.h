@@ -104,7 +104,8 @@ float oracle_hit_triangle(int conv, const float *o3, const float *d3, const floa
  */
 int oracle_render(const oprim *prims, const ouniforms *u, int conv, int math_mode, int threads,
                   uint32_t y0, uint32_t y1, const uint32_t *idx, uint64_t n_idx,
-                  float *accumulation, float *pixels, ovariance *variance, ocounters *counters);
+                  float *accumulation, float *pixels, ovariance *variance, ocounters *counters,
+                  uint64_t *samples_traced /* optional: ray_color calls made */);
 
 /* lib.rs:503-532: rows block of one frame.  mode 0 ASCII, 1 truecolor.  Returns bytes needed
  * (writes at most cap).  row_lengths (h entries) optional. */

@@ -73,6 +73,10 @@ class Timings(C.Structure):
                 ("kernel_launches", C.c_uint32), ("_pad", C.c_uint32)]
 
 
+class FrameStats(C.Structure):
+    _fields_ = [("samples_traced", C.c_uint64), ("bounces", C.c_uint64), ("pixels", C.c_uint64), ("reserved", C.c_uint64)]
+
+
 class CameraStruct(C.Structure):
     _fields_ = [("position", Vec3), ("yaw", C.c_float), ("pitch", C.c_float)]
 
@@ -109,6 +113,8 @@ SYMBOLS = {
     "trt_write_accumulation": (C.c_int, [_P, _P, C.c_size_t]),
     "trt_get_counters": (C.c_int, [_P, C.POINTER(Counters)]),
     "trt_get_timings": (C.c_int, [_P, C.POINTER(Timings)]),
+    "trt_get_frame_stats": (C.c_int, [_P, C.POINTER(FrameStats)]),
+    "trt_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "trt_device_buffer": (C.c_int, [_P, C.c_int, C.POINTER(_P), C.POINTER(C.c_size_t)]),
     "trt_cuda_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "trt_shard_rows": (C.c_uint32, [_P, C.c_uint32, _P, C.c_uint32]),
@@ -352,6 +358,11 @@ class Renderer:
         self._ck(lib().trt_get_timings(self.h, C.byref(t)))
         return t
 
+    def frame_stats(self) -> FrameStats:
+        st = FrameStats()
+        self._ck(lib().trt_get_frame_stats(self.h, C.byref(st)))
+        return st
+
     def device_buffer(self, which):
         p, n = _P(), C.c_size_t()
         self._ck(lib().trt_device_buffer(self.h, which, C.byref(p), C.byref(n)))
@@ -376,6 +387,15 @@ class Renderer:
                                              mode, C.byref(n) if want_len else None))
         self.size = (width, height)
         return n.value
+
+
+def measure_fp32_peak(device=0):
+    """(TFLOP/s measured by a register-resident FFMA loop, SM count, clock kHz)."""
+    tf, sm, khz = C.c_float(), C.c_int(), C.c_int()
+    rc = lib().trt_measure_fp32_peak(device, C.byref(tf), C.byref(sm), C.byref(khz))
+    if rc:
+        raise TrtError(rc, lib().trt_last_error(None).decode())
+    return tf.value, sm.value, khz.value
 
 
 def run(full_color: bool, verbose: bool, scene_path: str | None, **opts) -> int:

@@ -41,6 +41,7 @@ struct trt_ctx {
     trt_variance *d_variance = nullptr;
     unsigned long long *d_counters = nullptr;
     unsigned int *d_work = nullptr;
+    unsigned long long *d_stats = nullptr;
     uint32_t *d_row_map = nullptr;     // local row -> global row
     uint64_t *d_row_src = nullptr;     // quantiser source offsets per output row
     std::vector<uint32_t> rows;        // rows owned at `rows_height`
@@ -86,7 +87,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
-                    ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_row_map,
+                    ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map,
                     ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
@@ -134,6 +135,8 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         CK(cudaMalloc(&ctx->d_counters, K_COUNT * sizeof(unsigned long long)));
         CK(cudaMemsetAsync(ctx->d_counters, 0, K_COUNT * sizeof(unsigned long long), ctx->stream));
         CK(cudaMalloc(&ctx->d_work, 64));
+        CK(cudaMalloc(&ctx->d_stats, 64));
+        CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
         CK(cudaMalloc(&ctx->d_row_map, (size_t)cfg->max_height * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_src, (size_t)cfg->max_height * sizeof(uint64_t)));
         CK(cudaMalloc(&ctx->d_packed, ctx->max_pixels * sizeof(uint32_t)));
@@ -226,9 +229,9 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;
     ctx->lv.la = rp.la; ctx->lv.lb = rp.lb; ctx->lv.lc = rp.lc; ctx->lv.ln = rp.ln; ctx->lv.le = rp.le;
     CK(cudaStreamSynchronize(ctx->stream));
-    CK(persistent_scene_upload(ctx->sv, ctx->lv, ctx->stream));
     ctx->have_scene = true;
-    ctx->scene_serial++;
+    static unsigned long long g_scene_serial = 0;     // process-wide: a recycled ctx address never aliases
+    ctx->scene_serial = ++g_scene_serial;
     return TRT_OK;
 }
 
@@ -303,7 +306,8 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     fp.cam_up = make_float3(u->camera_up.x, u->camera_up.y, u->camera_up.z);
     fp.row_map = ctx->cfg.shard_count > 1u ? ctx->d_row_map : nullptr;
     fp.pixels = ctx->d_pixels; fp.accumulation = ctx->d_accum; fp.variance = ctx->d_variance;
-    fp.counters = ctx->d_counters; fp.work_counter = ctx->d_work;
+    fp.counters = ctx->d_counters; fp.work_counter = ctx->d_work; fp.stats = ctx->d_stats;
+    CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
     ctx->launches = 0;
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     if (fp.n_local_pixels) {
@@ -313,7 +317,8 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
             else trace_pixel_kernel<0, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
             ctx->launches += 1;
         } else {
-            cudaError_t e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream,
+            cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
+            if (e == cudaSuccess) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream,
                                                     &ctx->launches);
             if (e != cudaSuccess) { ctx->err = std::string("trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
         }
@@ -383,7 +388,6 @@ extern "C" int trt_quantise_gathered(trt_ctx *ctx, const void *d_gathered, size_
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaMemcpy(ctx->d_row_src, src.data(), height * sizeof(uint64_t), cudaMemcpyHostToDevice));
     ctx->rows_height = 0;      // d_row_src no longer describes this shard's rows
-    ctx->launches = 0;
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     int rc = launch_quantise(ctx, (const float4 *)d_gathered, ctx->d_row_src, width, height, mode);
     if (rc) return rc;
@@ -552,3 +556,73 @@ extern "C" int trt_alloc_host(size_t bytes, void **out) {
     return TRT_OK;
 }
 extern "C" void trt_free_host(void *p) { if (p) cudaFreeHost(p); }
+
+extern "C" int trt_get_frame_stats(trt_ctx *ctx, trt_frame_stats *out) {
+    if (!ctx || !out) return TRT_ERR_INVALID;
+    if (!ctx->have_frame) return fail(ctx, TRT_ERR_INVALID, "frame_stats before any frame was traced");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    unsigned long long h[2] = {0, 0};
+    CK(cudaMemcpy(h, ctx->d_stats, sizeof h, cudaMemcpyDeviceToHost));
+    out->samples_traced = h[0];
+    out->bounces = h[1];
+    out->pixels = (uint64_t)ctx->rows.size() * ctx->last_u.width;
+    out->reserved = 0;
+    return TRT_OK;
+}
+
+// ---- FP32 peak micro-benchmark -------------------------------------------------------------------------
+// 8 independent FFMA chains per thread, 1024 threads per SM-resident CTA pair: issue-bound on the FMA pipe.
+__global__ void __launch_bounds__(512) ffma_peak_kernel(float *out, int iters, float a, float b) {
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            x0 = __fmaf_rn(x0, a, b); x1 = __fmaf_rn(x1, a, b); x2 = __fmaf_rn(x2, a, b); x3 = __fmaf_rn(x3, a, b);
+            x4 = __fmaf_rn(x4, a, b); x5 = __fmaf_rn(x5, a, b); x6 = __fmaf_rn(x6, a, b); x7 = __fmaf_rn(x7, a, b);
+        }
+    }
+    float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == 12345.678f) out[0] = s;
+}
+
+extern "C" int trt_measure_fp32_peak(int device, float *tflops, int *sm_count, int *clock_khz) {
+    if (!tflops) return TRT_ERR_INVALID;
+    trt_ctx *ctx = nullptr;     // CK() target for error text
+    trt_ctx tmp;
+    ctx = &tmp;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) { cudaGetLastError(); g_create_err = "no CUDA device"; return TRT_ERR_NO_DEVICE; }
+    int rc = [&]() -> int {
+        CK(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, device));
+        if (sm_count) *sm_count = prop.multiProcessorCount;
+        if (clock_khz) *clock_khz = prop.clockRate;
+        float *d = nullptr;
+        CK(cudaMalloc(&d, 256));
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0));
+        CK(cudaEventCreate(&e1));
+        const int blocks = prop.multiProcessorCount * 4, iters = 4096;
+        float best = 0.0f;
+        for (int rep = 0; rep < 6; rep++) {
+            CK(cudaEventRecord(e0));
+            ffma_peak_kernel<<<blocks, 512>>>(d, iters, 1.0000001f, 1e-9f);
+            CK(cudaEventRecord(e1));
+            CK(cudaEventSynchronize(e1));
+            float ms = 0.0f;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            const double flops = 2.0 * 8 * 16 * (double)iters * 512.0 * blocks;
+            const float tf = (float)(flops / (ms * 1e-3) / 1e12);
+            if (rep >= 2 && tf > best) best = tf;
+        }
+        *tflops = best;
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        cudaFree(d);
+        return TRT_OK;
+    }();
+    if (rc) g_create_err = tmp.err;
+    return rc;
+}

@@ -41,6 +41,7 @@ struct FrameParams {
     trt_variance *variance;
     unsigned long long *counters;   // trt_counters as 19 x u64 (instrumented build only)
     unsigned int *work_counter;     // persistent kernel: next pixel to hand out
+    unsigned long long *stats;      // [0] samples traced, [1] closest-hit scans (bounces) of this frame
 };
 
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }

@@ -73,13 +73,14 @@ __global__ void repack_kernel(RepackParams rp) {
 template <int CONV, bool COUNT>
 __global__ void __launch_bounds__(128) trace_pixel_kernel(SceneView sc, LightView lv, FrameParams fp) {
     Counters<COUNT> cn;
-    Tracer<CONV, COUNT> tr(sc, lv, fp, cn);
+    Tracer<CONV, COUNT, SrcGlobal> tr(sc, lv, fp, cn);
     const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
     if (lp < fp.n_local_pixels) {
         const uint32_t lr = lp / fp.width, x = lp - lr * fp.width;
         const uint32_t y = fp.row_map ? fp.row_map[lr] : lr;
         tr.pixel(x, y);
     }
+    tr.flush_stats();
     if (COUNT) cn.flush(fp.counters);
 }
 

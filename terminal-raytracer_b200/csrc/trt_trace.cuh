@@ -11,16 +11,73 @@ struct LightView {               // emissive spheres / triangles in scan order (
     const float4 *le;            // (emission rgb, type as float bits)
 };
 
-template <int CONV, bool COUNT>
+// ---- where the scan reads geometry from -----------------------------------------------------------
+// Every lane of a warp tests the same primitive at the same time, so the geometry address is
+// warp-uniform.  Small scenes (Cornell box: 11 primitives) live in __constant__ memory: operands come
+// from the constant bank / uniform registers, no per-lane load, no load latency in the scan.
+// Large scenes (20 k primitives) are read from the SoA arrays in HBM through the read-only path
+// (one broadcast transaction per warp, L1/L2 resident: 0.85 MB).
+#define TRT_CONST_LIGHTS 16
+#define TRT_CONST_RUNS 16
+struct ConstScene {
+    float4 ga[TRT_CONST_PRIMS], gb[TRT_CONST_PRIMS], gc[TRT_CONST_PRIMS];
+    float4 la[TRT_CONST_LIGHTS], lb[TRT_CONST_LIGHTS], lc[TRT_CONST_LIGHTS], ln[TRT_CONST_LIGHTS], le[TRT_CONST_LIGHTS];
+    int4 runs[TRT_CONST_RUNS];
+};
+__constant__ ConstScene c_scene;
+
+struct SrcGlobal {
+    const SceneView &sc;
+    const LightView &lv;
+    __device__ SrcGlobal(const SceneView &s, const LightView &l) : sc(s), lv(l) {}
+    __device__ __forceinline__ float4 ga(int i) const { return __ldg(&sc.ga[i]); }
+    __device__ __forceinline__ float4 gb(int i) const { return __ldg(&sc.gb[i]); }
+    __device__ __forceinline__ float4 gc(int i) const { return __ldg(&sc.gc[i]); }
+    __device__ __forceinline__ int4 run(int r) const { return __ldg(&sc.runs[r]); }
+    __device__ __forceinline__ float4 la(int k) const { return __ldg(&lv.la[k]); }
+    __device__ __forceinline__ float4 lb(int k) const { return __ldg(&lv.lb[k]); }
+    __device__ __forceinline__ float4 lc(int k) const { return __ldg(&lv.lc[k]); }
+    __device__ __forceinline__ float4 ln(int k) const { return __ldg(&lv.ln[k]); }
+    __device__ __forceinline__ float4 le(int k) const { return __ldg(&lv.le[k]); }
+};
+struct SrcConst {
+    const SceneView &sc;
+    __device__ SrcConst(const SceneView &s, const LightView &) : sc(s) {}
+    __device__ __forceinline__ float4 ga(int i) const { return c_scene.ga[i]; }
+    __device__ __forceinline__ float4 gb(int i) const { return c_scene.gb[i]; }
+    __device__ __forceinline__ float4 gc(int i) const { return c_scene.gc[i]; }
+    __device__ __forceinline__ int4 run(int r) const { return c_scene.runs[r]; }
+    __device__ __forceinline__ float4 la(int k) const { return c_scene.la[k]; }
+    __device__ __forceinline__ float4 lb(int k) const { return c_scene.lb[k]; }
+    __device__ __forceinline__ float4 lc(int k) const { return c_scene.lc[k]; }
+    __device__ __forceinline__ float4 ln(int k) const { return c_scene.ln[k]; }
+    __device__ __forceinline__ float4 le(int k) const { return c_scene.le[k]; }
+};
+
+template <int CONV, bool COUNT, class SRC>
 struct Tracer {
     typedef M<CONV> V;
     const SceneView &sc;
-    const LightView &lv;
     const FrameParams &fp;
     Counters<COUNT> &cn;
+    SRC src;
+    uint32_t n_samples = 0, n_bounces = 0;      // always-on frame statistics (trt_frame_stats)
 
     __device__ Tracer(const SceneView &s, const LightView &l, const FrameParams &f, Counters<COUNT> &c)
-        : sc(s), lv(l), fp(f), cn(c) {}
+        : sc(s), fp(f), cn(c), src(s, l) {}
+
+    // warp-reduce the per-thread statistics and add them to the frame totals (all 32 lanes call this)
+    __device__ __forceinline__ void flush_stats() {
+        unsigned long long s = n_samples, b = n_bounces;
+        for (int o = 16; o > 0; o >>= 1) {
+            s += __shfl_xor_sync(0xffffffffu, s, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        if ((threadIdx.x & 31) == 0 && fp.stats) {
+            atomicAdd(&fp.stats[0], s);
+            atomicAdd(&fp.stats[1], b);
+        }
+    }
 
     // ---- single-primitive tests; `closest` is the current upper bound (shader.wgsl:258-277) -------
     // sphere: pre-reject shader.wgsl:260-269, then hit_sphere shader.wgsl:155-175 (oc == to_center,
@@ -79,6 +136,15 @@ struct Tracer {
         return -1.0f;
     }
 
+    __device__ __forceinline__ float test_any(int type, int i, float3 ro, float3 rd, float t_min, float closest,
+                                              uint32_t &cost) const {
+        cost = 0;
+        if (type == 0) return test_sphere(ro, rd, src.ga(i), src.gb(i).x, t_min, closest, cost);
+        if (type == 1) return test_plane(ro, rd, src.ga(i), src.gb(i), t_min, closest, cost);
+        if (type == 2) return test_triangle(ro, rd, src.ga(i), src.gb(i), src.gc(i), t_min, closest, cost);
+        return -1.0f;
+    }
+
     // ---- hit_scene as written (shader.wgsl:248-294): full scan, narrowing bound, first index wins
     // ties.  The record is completed once from the final (t, index) -- same values as updating it on
     // every improvement.  shadow_needed: -1 closest-hit scan; 0/1 shadow scan (counting only).
@@ -88,17 +154,10 @@ struct Tracer {
         best = -1;
         bool found = false;
         for (int r = 0; r < sc.n_runs; r++) {
-            int4 run = __ldg(&sc.runs[r]);
+            const int4 run = src.run(r);
             for (int i = run.y; i < run.z; i++) {
-                float t = -1.0f;
-                uint32_t cost = 0;
-                if (run.x == 0) {
-                    t = test_sphere(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]).x, t_min, closest, cost);
-                } else if (run.x == 1) {
-                    t = test_plane(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), t_min, closest, cost);
-                } else if (run.x == 2) {
-                    t = test_triangle(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), __ldg(&sc.gc[i]), t_min, closest, cost);
-                }
+                uint32_t cost;
+                const float t = test_any(run.x, i, ro, rd, t_min, closest, cost);
                 if (COUNT) {
                     cn.add(K_PRIM_TESTS, 1);
                     cn.add(K_FLOPS_WRITTEN, cost);
@@ -130,21 +189,19 @@ struct Tracer {
     // (shader.wgsl:400-402), and before the first accepted hit the bound is still t_max, so stopping at
     // the first accepted primitive returns the same truth value.
     __device__ __forceinline__ bool scan_any(float3 ro, float3 rd, float t_min, float t_max) {
-        uint32_t cost;
         for (int r = 0; r < sc.n_runs; r++) {
-            int4 run = __ldg(&sc.runs[r]);
+            const int4 run = src.run(r);
             for (int i = run.y; i < run.z; i++) {
-                float t = -1.0f;
-                if (run.x == 0) t = test_sphere(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]).x, t_min, t_max, cost);
-                else if (run.x == 1) t = test_plane(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), t_min, t_max, cost);
-                else if (run.x == 2) t = test_triangle(ro, rd, __ldg(&sc.ga[i]), __ldg(&sc.gb[i]), __ldg(&sc.gc[i]), t_min, t_max, cost);
+                uint32_t cost;
+                const float t = test_any(run.x, i, ro, rd, t_min, t_max, cost);
                 if (t > 0.0f && t < t_max) return true;
             }
         }
         return false;
     }
 
-    // shader.wgsl:234-245 (plane / triangle normals precomputed with the same operations)
+    // shader.wgsl:234-245 (plane / triangle normals precomputed with the same operations); the index is
+    // lane-divergent here, so these come from HBM/L1 through the read-only path
     __device__ __forceinline__ float3 normal_at(int i, int type, float3 p) const {
         if (type == 0) {
             float4 a = __ldg(&sc.ga[i]);
@@ -184,10 +241,10 @@ struct Tracer {
                                                       float3 attenuation) {
         float3 direct = f3(0.0f, 0.0f, 0.0f);
         for (int k = 0; k < sc.n_lights; k++) {
-            float4 a = __ldg(&lv.la[k]);
-            float4 nl = __ldg(&lv.ln[k]);
-            float4 em = __ldg(&lv.le[k]);
-            int type = __float_as_int(em.w);
+            const float4 a = src.la(k);
+            const float4 nl = src.ln(k);
+            const float4 em = src.le(k);
+            const int type = __float_as_int(em.w);
             float3 light_point, light_normal;
             float r1 = rnd(rng), r2 = rnd(rng);
             if (COUNT) cn.add(K_RNG_DRAWS, 2);
@@ -205,7 +262,7 @@ struct Tracer {
                 float sqrt_r1 = sqrtf(r1);
                 float u = 1.0f - sqrt_r1;
                 float v = r2 * sqrt_r1;
-                light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(__ldg(&lv.lb[k])), u, xyz(__ldg(&lv.lc[k])), v);
+                light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(src.lb(k)), u, xyz(src.lc(k)), v);
                 light_normal = xyz(nl);
                 if (COUNT) cn.flops(60);
             }
@@ -242,49 +299,56 @@ struct Tracer {
         return direct;
     }
 
+    // One iteration of the bounce loop shader.wgsl:444-493 (i = bounce index).  Returns true when the
+    // path ends here (miss or roulette); the caller also stops at i + 1 == max_depth.
+    __device__ __forceinline__ bool bounce(uint32_t &rng, float3 &ro, float3 &rd, float3 &att, float3 &acc, uint32_t i) {
+        int idx;
+        n_bounces++;
+        if (COUNT) cn.add(K_CLOSEST_SCANS, 1);
+        const float t = scan_closest(ro, rd, 0.001f, 1e10f, idx, -1);
+        if (t < 0.0f) {
+            if (COUNT) { cn.add(K_MISSES, 1); cn.flops(21); }
+            acc = V::vmad(acc, sky(rd), att);
+            return true;
+        }
+        if (COUNT) { cn.add(K_HITS, 1); cn.flops(9); }
+        const float4 mc = __ldg(&sc.mc[idx]);
+        const float4 me = __ldg(&sc.me[idx]);
+        const int type = __float_as_int(me.w);
+        const float3 p = V::axpy(ro, rd, t);
+        float3 n = normal_at(idx, type, p);
+        if (!(V::dot(rd, n) < 0.0f)) n = V::scale(n, -1.0f);
+        acc = V::vmad(acc, xyz(me), att);
+        acc = V::add(acc, direct_lighting(rng, p, n, xyz(mc), att));
+        float3 scatter;
+        if (COUNT) cn.add(K_RNG_DRAWS, 1);
+        if (mc.w > rnd(rng)) {
+            if (COUNT) { cn.add(K_MIRROR, 1); cn.flops(12); }
+            scatter = V::reflect(rd, n);
+        } else {
+            if (COUNT) { cn.add(K_DIFFUSE, 1); cn.flops(75); }
+            scatter = cosine_hemisphere(rng, n);
+        }
+        att = V::mulv(att, xyz(mc));
+        if (COUNT) cn.flops(9);
+        ro = V::axpy(p, scatter, 0.001f);
+        rd = scatter;
+        if (i > 3u) {
+            float survival = fminf(0.95f, fmaxf(att.x, fmaxf(att.y, att.z)));
+            if (COUNT) { cn.add(K_ROULETTE_TESTS, 1); cn.add(K_RNG_DRAWS, 1); }
+            if (survival < rnd(rng)) { if (COUNT) cn.add(K_ROULETTE_KILLS, 1); return true; }
+            if (COUNT) cn.flops(3);
+            att = V::divs(att, survival);
+        }
+        return false;
+    }
+
     // shader.wgsl:439-495
     __device__ __forceinline__ float3 ray_color(uint32_t &rng, float3 ro, float3 rd) {
         float3 acc = f3(0.0f, 0.0f, 0.0f);
         float3 att = f3(1.0f, 1.0f, 1.0f);
-        for (uint32_t i = 0; i < fp.max_depth; i++) {
-            int idx;
-            if (COUNT) cn.add(K_CLOSEST_SCANS, 1);
-            float t = scan_closest(ro, rd, 0.001f, 1e10f, idx, -1);
-            if (t < 0.0f) {
-                if (COUNT) { cn.add(K_MISSES, 1); cn.flops(21); }
-                acc = V::vmad(acc, sky(rd), att);
-                break;
-            }
-            if (COUNT) { cn.add(K_HITS, 1); cn.flops(9); }
-            float4 mc = __ldg(&sc.mc[idx]);
-            float4 me = __ldg(&sc.me[idx]);
-            int type = __float_as_int(me.w);
-            float3 p = V::axpy(ro, rd, t);
-            float3 n = normal_at(idx, type, p);
-            if (!(V::dot(rd, n) < 0.0f)) n = V::scale(n, -1.0f);
-            acc = V::vmad(acc, xyz(me), att);
-            acc = V::add(acc, direct_lighting(rng, p, n, xyz(mc), att));
-            float3 scatter;
-            if (COUNT) cn.add(K_RNG_DRAWS, 1);
-            if (mc.w > rnd(rng)) {
-                if (COUNT) { cn.add(K_MIRROR, 1); cn.flops(12); }
-                scatter = V::reflect(rd, n);
-            } else {
-                if (COUNT) { cn.add(K_DIFFUSE, 1); cn.flops(75); }
-                scatter = cosine_hemisphere(rng, n);
-            }
-            att = V::mulv(att, xyz(mc));
-            if (COUNT) cn.flops(9);
-            ro = V::axpy(p, scatter, 0.001f);
-            rd = scatter;
-            if (i > 3u) {
-                float survival = fminf(0.95f, fmaxf(att.x, fmaxf(att.y, att.z)));
-                if (COUNT) { cn.add(K_ROULETTE_TESTS, 1); cn.add(K_RNG_DRAWS, 1); }
-                if (survival < rnd(rng)) { if (COUNT) cn.add(K_ROULETTE_KILLS, 1); break; }
-                if (COUNT) cn.flops(3);
-                att = V::divs(att, survival);
-            }
-        }
+        for (uint32_t i = 0; i < fp.max_depth; i++)
+            if (bounce(rng, ro, rd, att, acc, i)) break;
         return acc;
     }
 
@@ -301,40 +365,48 @@ struct Tracer {
         ro = fp.cam_pos;
     }
 
+    // shader.wgsl:555-562: variance of the base samples and the number of adaptive extra samples
+    __device__ __forceinline__ uint32_t adaptive_extra(float3 color_sum, float3 sq_sum, float &variance_value) const {
+        float3 mean = V::divs(color_sum, fp.base_f);
+        float3 var_vec = V::sub(V::divs(sq_sum, fp.base_f), V::mulv(mean, mean));
+        variance_value = var_vec.x + var_vec.y + var_vec.z;
+        if (variance_value > 10.0f && fp.base_samples < fp.spp)
+            return min(fp.spp - fp.base_samples, __float2uint_rz(variance_value * 50.0f));
+        return 0u;
+    }
+
     // shader.wgsl:499-621 for one pixel
     __device__ __forceinline__ void pixel(uint32_t x, uint32_t y) {
         uint32_t rng = (y * fp.width + x) * 1973u + fp.seed * 9277u + fp.frame_number * 12345u;
-        float3 pixel_color = f3(0, 0, 0), color_sum = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
-        const uint32_t base = fp.base_samples, max_samples = fp.spp;
+        float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
+        const uint32_t base = fp.base_samples;
         if (COUNT) { cn.add(K_PIXELS, 1); cn.flops(30); }
         for (uint32_t i = 0; i < base; i++) {
             rng = pcg_hash(rng + i * 5096u);
             float3 ro, rd;
             camera_ray(rng, x, y, ro, rd);
             float3 c = ray_color(rng, ro, rd);
-            pixel_color = V::add(pixel_color, c);
-            color_sum = V::add(color_sum, c);
+            n_samples++;
+            pixel_color = V::add(pixel_color, c);        // color_sum == pixel_color during the base samples (:549-550)
             sq_sum = V::add(sq_sum, V::mulv(c, c));
             if (COUNT) { cn.add(K_SAMPLES_BASE, 1); cn.flops(50); }
         }
-        float3 mean = V::divs(color_sum, fp.base_f);
-        float3 var_vec = V::sub(V::divs(sq_sum, fp.base_f), V::mulv(mean, mean));
-        float variance_value = var_vec.x + var_vec.y + var_vec.z;
-        if (variance_value > 10.0f && base < max_samples) {
-            uint32_t additional = min(max_samples - base, __float2uint_rz(variance_value * 50.0f));
-            for (uint32_t i = 0; i < additional; i++) {
-                rng = pcg_hash(rng + (base + i) * 5096u);
-                float3 ro, rd;
-                camera_ray(rng, x, y, ro, rd);
-                pixel_color = V::add(pixel_color, ray_color(rng, ro, rd));
-                if (COUNT) { cn.add(K_SAMPLES_EXTRA, 1); cn.flops(41); }
-            }
-            pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(base + additional));
+        float variance_value;
+        const uint32_t additional = adaptive_extra(pixel_color, sq_sum, variance_value);
+        const bool adaptive = variance_value > 10.0f && base < fp.spp;
+        for (uint32_t i = 0; i < additional; i++) {
+            rng = pcg_hash(rng + (base + i) * 5096u);
+            float3 ro, rd;
+            camera_ray(rng, x, y, ro, rd);
+            pixel_color = V::add(pixel_color, ray_color(rng, ro, rd));
+            n_samples++;
+            if (COUNT) { cn.add(K_SAMPLES_EXTRA, 1); cn.flops(41); }
         }
+        if (adaptive) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(base + additional));
         finish_pixel(x, y, pixel_color, variance_value);
     }
 
-    // shader.wgsl:605-621: variance store, temporal accumulation, pixel store (float4, coalesced)
+    // shader.wgsl:605-621: variance store, temporal accumulation, pixel store (one float4 per buffer)
     __device__ __forceinline__ void finish_pixel(uint32_t x, uint32_t y, float3 pixel_color, float variance_value) {
         size_t index = (size_t)y * fp.width + x;
         trt_variance vb;
