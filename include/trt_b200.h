@@ -161,6 +161,10 @@ int trt_get_frame_stats(trt_ctx *ctx, trt_frame_stats *out);
 /* register-resident FFMA loop on every SM: the measured FP32 FMA peak of this GPU in TFLOP/s
  * (roofline denominator cross-check; nominal = SMs x 128 lanes x 2 x clock) */
 int trt_measure_fp32_peak(int device, float *tflops, int *sm_count, int *clock_khz);
+/* device self-test: the kernels' shared-reciprocal vec3 division against the IEEE `/` operator on
+ * n_cases pseudo-random (a.x, a.y, a.z, s) tuples; distribution 0 raw bits, 1 scene-like, 2 mantissa
+ * corner cases.  *mismatches = components whose bits differ (NaN == NaN). */
+int trt_selftest_div3(int device, uint64_t n_cases, uint32_t seed, int distribution, uint64_t *mismatches, float *first_bad4);
 
 /* multi-GPU plumbing: raw device pointers of this context's buffers so that the host driver can
  * hand them to NCCL (gather of the shards' pixel rows), and a quantise that reads a caller-owned

@@ -13,7 +13,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libtrt_b200.so")
+# TRT_B200_LIB selects an experimental build of the same library (kernel tuning A/B runs)
+LIB_PATH = os.environ.get("TRT_B200_LIB") or os.path.join(HERE, "libtrt_b200.so")
 
 TRT_ABI_VERSION = 1
 CONV_AS_WRITTEN, CONV_FUSED = 0, 1
@@ -115,6 +116,7 @@ SYMBOLS = {
     "trt_get_timings": (C.c_int, [_P, C.POINTER(Timings)]),
     "trt_get_frame_stats": (C.c_int, [_P, C.POINTER(FrameStats)]),
     "trt_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "trt_selftest_div3": (C.c_int, [C.c_int, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_float)]),
     "trt_device_buffer": (C.c_int, [_P, C.c_int, C.POINTER(_P), C.POINTER(C.c_size_t)]),
     "trt_cuda_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "trt_shard_rows": (C.c_uint32, [_P, C.c_uint32, _P, C.c_uint32]),
@@ -387,6 +389,15 @@ class Renderer:
                                              mode, C.byref(n) if want_len else None))
         self.size = (width, height)
         return n.value
+
+
+def selftest_div3(n_cases, seed=1, distribution=0, device=0):
+    """(mismatching components, (a, s, a/s expected, got) of the first one)"""
+    bad, first = C.c_uint64(), (C.c_float * 4)()
+    rc = lib().trt_selftest_div3(device, n_cases, seed, distribution, C.byref(bad), first)
+    if rc:
+        raise TrtError(rc, lib().trt_last_error(None).decode())
+    return bad.value, tuple(first)
 
 
 def measure_fp32_peak(device=0):

@@ -9,6 +9,7 @@
 
 #include "trt_kernels.cuh"
 #include "trt_persistent.cuh"
+#include "trt_wave.cuh"
 #include "trt_quantise.cuh"
 
 using namespace trt;
@@ -271,6 +272,7 @@ static int ensure_rows(trt_ctx *ctx, uint32_t w, uint32_t h) {
 static int check_uniforms(trt_ctx *ctx, const trt_uniforms *u) {
     if (!u) return fail(ctx, TRT_ERR_INVALID, "null uniforms");
     if (!ctx->have_scene) return fail(ctx, TRT_ERR_NO_SCENE, "render before trt_upload_scene");
+    if (u->width > 65535u || u->height > 65535u) return fail(ctx, TRT_ERR_INVALID, "uniforms: frame larger than 65535 in a dimension");
     if (u->width == 0 || u->height == 0 || u->width > ctx->cfg.max_width || u->height > ctx->cfg.max_height ||
         (size_t)u->width * u->height > ctx->max_pixels)
         return fail(ctx, TRT_ERR_INVALID, "uniforms: frame size is zero or exceeds trt_config.max_width/max_height");
@@ -318,8 +320,13 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
             ctx->launches += 1;
         } else {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
-            if (e == cudaSuccess) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream,
-                                                    &ctx->launches);
+            // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)
+            static const bool use_v1 = [] { const char *k = getenv("TRT_B200_KERNEL"); return k && !strcmp(k, "v1"); }();
+            if (e == cudaSuccess) {
+                if (use_v1) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream, &ctx->launches);
+                else e = wave_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, scene_fits_constant(ctx->sv),
+                                           ctx->stream, &ctx->launches);
+            }
             if (e != cudaSuccess) { ctx->err = std::string("trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
         }
         CK(cudaGetLastError());
@@ -621,6 +628,67 @@ extern "C" int trt_measure_fp32_peak(int device, float *tflops, int *sm_count, i
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         cudaFree(d);
+        return TRT_OK;
+    }();
+    if (rc) g_create_err = tmp.err;
+    return rc;
+}
+
+// ---- self-test of div3_rn against the IEEE `/` operator (tests/test_gpu_division.py) ---------------------
+__device__ __forceinline__ uint32_t mix32(uint32_t v) { v ^= v >> 16; v *= 0x7feb352du; v ^= v >> 15; v *= 0x846ca68bu; v ^= v >> 16; return v; }
+__global__ void div3_selftest_kernel(unsigned long long n, uint32_t seed, int dist, unsigned long long *mismatch, float *first_bad) {
+    unsigned long long bad = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        uint32_t h = mix32((uint32_t)i * 4u + seed), g = mix32((uint32_t)(i >> 32) + 0x9e3779b9u * ((uint32_t)i * 4u + 1u) + seed);
+        uint32_t b[4] = {h, mix32(h + g), mix32(g ^ 0x85ebca6bu), mix32(h * 3u + g)};
+        float v[4];
+        for (int c = 0; c < 4; c++) {
+            uint32_t bits = b[c];
+            if (dist == 1) {            // scene-like magnitudes: exponent in [2^-24, 2^8), some exact zeros
+                bits = (bits & 0x807fffffu) | ((103u + (b[(c + 1) & 3] >> 27)) << 23);
+                if ((b[(c + 2) & 3] & 15u) == 0u && c < 3) bits &= 0x80000000u;
+            } else if (dist == 2) {     // mantissa corner cases
+                const uint32_t m[8] = {0u, 1u, 0x7fffffu, 0x7ffffeu, 0x400000u, 0x3fffffu, 0x555555u, 0x2aaaaau};
+                bits = (bits & 0x80000000u) | ((120u + ((bits >> 8) & 15u)) << 23) | m[bits & 7u];
+            }                           // dist 0: raw random bits (NaN, inf, denormals included)
+            v[c] = __uint_as_float(bits);
+        }
+        const float3 got = div3_rn(make_float3(v[0], v[1], v[2]), v[3]);
+        const float ex[3] = {v[0] / v[3], v[1] / v[3], v[2] / v[3]}, gt[3] = {got.x, got.y, got.z};
+        for (int c = 0; c < 3; c++) {
+            const bool same = (__float_as_uint(ex[c]) == __float_as_uint(gt[c])) || (ex[c] != ex[c] && gt[c] != gt[c]);
+            if (!same) {
+                if (bad == 0 && atomicAdd(mismatch + 1, 1ull) == 0ull) { first_bad[0] = v[c]; first_bad[1] = v[3]; first_bad[2] = ex[c]; first_bad[3] = gt[c]; }
+                bad++;
+            }
+        }
+    }
+    if (bad) atomicAdd(mismatch, bad);
+}
+
+extern "C" int trt_selftest_div3(int device, uint64_t n_cases, uint32_t seed, int distribution, uint64_t *mismatches, float *first_bad4) {
+    if (!mismatches) return TRT_ERR_INVALID;
+    trt_ctx tmp;
+    trt_ctx *ctx = &tmp;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) { cudaGetLastError(); g_create_err = "no CUDA device"; return TRT_ERR_NO_DEVICE; }
+    int rc = [&]() -> int {
+        CK(cudaSetDevice(device));
+        unsigned long long *d = nullptr;
+        float *fb = nullptr;
+        CK(cudaMalloc(&d, 16));
+        CK(cudaMalloc(&fb, 16));
+        CK(cudaMemset(d, 0, 16));
+        CK(cudaMemset(fb, 0, 16));
+        div3_selftest_kernel<<<148 * 8, 256>>>(n_cases, seed, distribution, d, fb);
+        CK(cudaGetLastError());
+        CK(cudaDeviceSynchronize());
+        unsigned long long h[2];
+        CK(cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost));
+        if (first_bad4) CK(cudaMemcpy(first_bad4, fb, 16, cudaMemcpyDeviceToHost));
+        *mismatches = h[0];
+        cudaFree(d);
+        cudaFree(fb);
         return TRT_OK;
     }();
     if (rc) g_create_err = tmp.err;

@@ -47,13 +47,48 @@ struct FrameParams {
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 __device__ __forceinline__ float3 xyz(float4 v) { return make_float3(v.x, v.y, v.z); }
 
+// ---- correctly rounded division of three numerators by one divisor -------------------------------
+// vec3_div (shader.wgsl:99-101) is `a.x / s, a.y / s, a.z / s`: three IEEE divisions.  Compiled as
+// written, each one is MUFU.RCP + Newton steps + FCHK, and FCHK sends every zero numerator (axis-
+// aligned normals: most of the Cornell box) to a ~60-instruction slow-path subroutine (ncu:
+// profiles/r1_trace_wave_pre_div.txt, 32 % of all instructions).  div3_rn computes the same three
+// correctly rounded quotients with ONE reciprocal:
+//     y  = rcp(s) refined once           (error < 1 ulp)
+//     q0 = RN(a*y);  r = a - s*q0 (exact, FMA);  q = RN(q0 + r*y)      -- Markstein's correction step
+// which is RN(a/s) whenever a, s and a/s are normal numbers away from the exponent limits, and keeps
+// the signed zero of a zero numerator (q0).  Anything else (tiny, huge, infinite, NaN) goes to the
+// plain IEEE division in div3_slow.  tests/test_gpu_division.py checks it against `/` bit for bit.
+__device__ __noinline__ float3 div3_slow(float ax, float ay, float az, float s) { return make_float3(ax / s, ay / s, az / s); }
+
+__device__ __forceinline__ float3 div3_rn(float3 a, float s) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(s));
+    y = __fmaf_rn(y, __fmaf_rn(-s, y, 1.0f), y);
+    const float qx = a.x * y, qy = a.y * y, qz = a.z * y;
+    float ox = __fmaf_rn(__fmaf_rn(-s, qx, a.x), y, qx);
+    float oy = __fmaf_rn(__fmaf_rn(-s, qy, a.y), y, qy);
+    float oz = __fmaf_rn(__fmaf_rn(-s, qz, a.z), y, qz);
+    ox = (a.x == 0.0f) ? qx : ox;
+    oy = (a.y == 0.0f) ? qy : oy;
+    oz = (a.z == 0.0f) ? qz : oz;
+    // guard: |s| in [2^-40, 2^40); every numerator is zero or has |a| in [2^-60, 2^60)
+    // (bits << 1 drops the sign; "- 1" sends zero to 0xffffffff so that it passes the lower bound)
+    const uint32_t us = __float_as_uint(s) << 1;
+    const uint32_t ux = (__float_as_uint(a.x) << 1) - 1u, uy = (__float_as_uint(a.y) << 1) - 1u, uz = (__float_as_uint(a.z) << 1) - 1u;
+    const uint32_t lo = min(min(ux, uy), uz);
+    const float big = fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fabsf(a.z));
+    const bool ok = (us - 0x57000000u < 0x50000000u) && lo >= 0x43000000u - 1u && big < 1.152921504606846976e18f;
+    if (!ok) return div3_slow(a.x, a.y, a.z, s);
+    return make_float3(ox, oy, oz);
+}
+
 // ---- vector helpers (shader.wgsl:83-101,126-140,225-232) ----------------------------------------
 template <int CONV> struct M {
     static __device__ __forceinline__ float3 add(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
     static __device__ __forceinline__ float3 sub(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
     static __device__ __forceinline__ float3 scale(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
     static __device__ __forceinline__ float3 mulv(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
-    static __device__ __forceinline__ float3 divs(float3 a, float s) { return f3(a.x / s, a.y / s, a.z / s); }
+    static __device__ __forceinline__ float3 divs(float3 a, float s) { return div3_rn(a, s); }     // == a.x/s, a.y/s, a.z/s
     static __device__ __forceinline__ float dot(float3 a, float3 b) {
         if (CONV) return __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, a.x * b.x));
         return a.x * b.x + a.y * b.y + a.z * b.z;

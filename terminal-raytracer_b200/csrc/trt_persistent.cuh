@@ -18,8 +18,12 @@
 
 namespace trt {
 
+#ifndef TRT_PT_THREADS
 #define TRT_PT_THREADS 128
+#endif
+#ifndef TRT_PT_CTAS_PER_SM
 #define TRT_PT_CTAS_PER_SM 4
+#endif
 
 enum { ST_NEED_PIXEL = 0, ST_NEED_SAMPLE = 1, ST_TRACE = 2, ST_DONE = 3 };
 

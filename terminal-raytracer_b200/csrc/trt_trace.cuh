@@ -155,6 +155,7 @@ struct Tracer {
         bool found = false;
         for (int r = 0; r < sc.n_runs; r++) {
             const int4 run = src.run(r);
+#pragma unroll 1                        // one copy of each test: the loop body must stay inside the instruction cache
             for (int i = run.y; i < run.z; i++) {
                 uint32_t cost;
                 const float t = test_any(run.x, i, ro, rd, t_min, closest, cost);
@@ -191,6 +192,7 @@ struct Tracer {
     __device__ __forceinline__ bool scan_any(float3 ro, float3 rd, float t_min, float t_max) {
         for (int r = 0; r < sc.n_runs; r++) {
             const int4 run = src.run(r);
+#pragma unroll 1                        // one copy of each test: the loop body must stay inside the instruction cache
             for (int i = run.y; i < run.z; i++) {
                 uint32_t cost;
                 const float t = test_any(run.x, i, ro, rd, t_min, t_max, cost);
