@@ -97,6 +97,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         float t_hit = -1.0f;
         if (mode != WM_DONE && fp.max_depth != 0u) t_hit = tr.scan_closest(ro, rd, 0.001f, t_max, best, -1);
 
+        __syncwarp();
         bool path_end = false;
         bool lights = false;
         if (mode == WM_CLOSEST) {
@@ -127,10 +128,15 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         }
 
         // ---- light loop (shader.wgsl:342-433), resumable at light k --------------------------------------------
-        bool scatter = false;
-        if (lights) {
-            mode = WM_CLOSEST;
-            while (k < sc.n_lights) {
+        // Warp-uniform trip structure: lanes sit at different k, every trip serves all lanes that still
+        // have a light to sample, and the warp reconverges before each trip and before the scatter step
+        // (without the votes the compiler lets early leavers run ahead and the scatter code then
+        // executes once per leaving group: profiles/r1_trace_wave2_by_line.txt).
+        if (lights) mode = WM_CLOSEST;
+        for (;;) {
+            const bool in_loop = lights && mode == WM_CLOSEST && k < sc.n_lights;
+            if (!__any_sync(0xffffffffu, in_loop)) break;
+            if (in_loop) {
                 const float4 a = tr.src.la(k);
                 const float4 nl = tr.src.ln(k);
                 const float4 em = tr.src.le(k);
@@ -166,12 +172,13 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     rd = light_dir;
                     t_max = light_distance - 0.001f;
                     mode = WM_SHADOW;
-                    break;
+                } else {
+                    k++;                                          // a scan that cannot change the sum is skipped
                 }
-                k++;                                              // a scan that cannot change the sum is skipped
             }
-            scatter = (mode == WM_CLOSEST);
         }
+        const bool scatter = lights && mode == WM_CLOSEST;
+        __syncwarp();
 
         // ---- scatter + roulette (shader.wgsl:459-492) ---------------------------------------------------------------
         if (scatter) {
@@ -193,6 +200,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         }
 
         // ---- sample / pixel bookkeeping (shader.wgsl:548-551, :555-565, :596-621) --------------------------------------
+        __syncwarp();
         if (path_end) {
             tr.n_samples++;
             pixel_color = V::add(pixel_color, acc);
