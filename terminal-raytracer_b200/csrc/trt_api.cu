@@ -171,11 +171,42 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     for (uint32_t i = 0; i < count; i++) {
         const uint32_t t = prims[i].primitive_type;
         types[i] = t <= 2u ? (uint8_t)t : (uint8_t)255;
-        if (runs.empty() || runs.back().x != (int)types[i]) runs.push_back(make_int4((int)types[i], (int)i, (int)i + 1, 0));
-        else runs.back().z = (int)i + 1;
+        if (t == 1u) {
+            // axis-aligned plane: the normal is exactly +-1 on one axis and +-0 on the others and the point
+            // is below 1e30 in magnitude (p - o cannot overflow); then dot(n, d) == +-d_axis and dot(p - o, n) == +-(p_axis - o_axis) bit for bit
+            // for finite rays (scan_lean, trt_trace.cuh).  Device-side run types 3, 4, 5 = x, y, z.
+            const float n[3] = {prims[i].plane_normal.x, prims[i].plane_normal.y, prims[i].plane_normal.z};
+            const float p[3] = {prims[i].plane_point.x, prims[i].plane_point.y, prims[i].plane_point.z};
+            int ones = 0, zeros = 0, axis = 0;
+            for (int c = 0; c < 3; c++) {
+                if (n[c] == 1.0f || n[c] == -1.0f) { ones++; axis = c; }
+                else if (n[c] == 0.0f) zeros++;
+            }
+            if (ones == 1 && zeros == 2 && std::fabs(p[0]) < 1e30f && std::fabs(p[1]) < 1e30f && std::fabs(p[2]) < 1e30f)
+                types[i] = (uint8_t)(3 + axis);
+        }
         // shader.wgsl:346-347 light test, :352/:370 supported light types
         const float power = prims[i].emission.x + prims[i].emission.y + prims[i].emission.z;
         if (power > 0.001f && (t == 0u || t == 2u)) light_prim.push_back((int)i);
+    }
+    // slab pairs: two consecutive axis-aligned planes of the same axis at different positions (device run
+    // types 6, 7, 8); gc of the first plane holds (p_lo, p_hi, first-plane-is-p_hi, 2^20 * gap) for scan_lean
+    struct PairInfo { uint32_t index; float4 v; };
+    std::vector<PairInfo> pairs;
+    for (uint32_t i = 0; i + 1 < count; i++) {
+        if (types[i] < 3 || types[i] > 5 || types[i + 1] != types[i]) continue;
+        const int axis = types[i] - 3;
+        const float p0 = (&prims[i].plane_point.x)[axis], p1 = (&prims[i + 1].plane_point.x)[axis];
+        if (p0 == p1) continue;
+        const float lo = p0 < p1 ? p0 : p1, hi = p0 < p1 ? p1 : p0;
+        pairs.push_back({i, make_float4(lo, hi, p0 < p1 ? 0.0f : 1.0f, 1048576.0f * (hi - lo))});
+        types[i] = types[i + 1] = (uint8_t)(6 + axis);
+        i++;
+    }
+    for (uint32_t i = 0; i < count; i++) {
+        // a pair run must start on a pair boundary: never merge a pair run into a preceding one of odd length
+        if (runs.empty() || runs.back().x != (int)types[i]) runs.push_back(make_int4((int)types[i], (int)i, (int)i + 1, 0));
+        else runs.back().z = (int)i + 1;
     }
     const uint32_t n_lights = (uint32_t)light_prim.size(), n_runs = (uint32_t)runs.size();
     CK(cudaStreamSynchronize(ctx->stream));
@@ -225,6 +256,8 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
         else repack_kernel<0><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
         CK(cudaGetLastError());
     }
+    for (const PairInfo &pi : pairs)
+        CK(cudaMemcpyAsync(rp.gc + pi.index, &pi.v, sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     ctx->sv.ga = rp.ga; ctx->sv.gb = rp.gb; ctx->sv.gc = rp.gc; ctx->sv.gn = rp.gn; ctx->sv.mc = rp.mc; ctx->sv.me = rp.me;
     ctx->sv.type = ctx->d_type; ctx->sv.runs = ctx->d_runs; ctx->sv.lights = ctx->d_lights;
     ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;

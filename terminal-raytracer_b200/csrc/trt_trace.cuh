@@ -33,6 +33,7 @@ struct SrcGlobal {
     __device__ __forceinline__ float4 ga(int i) const { return __ldg(&sc.ga[i]); }
     __device__ __forceinline__ float4 gb(int i) const { return __ldg(&sc.gb[i]); }
     __device__ __forceinline__ float4 gc(int i) const { return __ldg(&sc.gc[i]); }
+    __device__ __forceinline__ float ga_axis(int i, int axis) const { return __ldg(reinterpret_cast<const float *>(&sc.ga[i]) + axis); }
     __device__ __forceinline__ int4 run(int r) const { return __ldg(&sc.runs[r]); }
     __device__ __forceinline__ float4 la(int k) const { return __ldg(&lv.la[k]); }
     __device__ __forceinline__ float4 lb(int k) const { return __ldg(&lv.lb[k]); }
@@ -46,6 +47,7 @@ struct SrcConst {
     __device__ __forceinline__ float4 ga(int i) const { return c_scene.ga[i]; }
     __device__ __forceinline__ float4 gb(int i) const { return c_scene.gb[i]; }
     __device__ __forceinline__ float4 gc(int i) const { return c_scene.gc[i]; }
+    __device__ __forceinline__ float ga_axis(int i, int axis) const { return reinterpret_cast<const float *>(&c_scene.ga[i])[axis]; }
     __device__ __forceinline__ int4 run(int r) const { return c_scene.runs[r]; }
     __device__ __forceinline__ float4 la(int k) const { return c_scene.la[k]; }
     __device__ __forceinline__ float4 lb(int k) const { return c_scene.lb[k]; }
@@ -140,7 +142,7 @@ struct Tracer {
                                               uint32_t &cost) const {
         cost = 0;
         if (type == 0) return test_sphere(ro, rd, src.ga(i), src.gb(i).x, t_min, closest, cost);
-        if (type == 1) return test_plane(ro, rd, src.ga(i), src.gb(i), t_min, closest, cost);
+        if (type == 1 || (type >= 3 && type <= 8)) return test_plane(ro, rd, src.ga(i), src.gb(i), t_min, closest, cost);   // 3..8: axis-aligned planes / slab pairs
         if (type == 2) return test_triangle(ro, rd, src.ga(i), src.gb(i), src.gc(i), t_min, closest, cost);
         return -1.0f;
     }
@@ -175,11 +177,108 @@ struct Tracer {
                         float3 p = V::axpy(ro, rd, t);
                         float3 n = normal_at(i, run.x, p);
                         bool front = V::dot(rd, n) < 0.0f;
-                        uint32_t hc = 6u + (run.x == 0 ? 15u : run.x == 1 ? 9u : 24u) + 5u + (front ? 0u : 3u);
+                        uint32_t hc = 6u + (run.x == 0 ? 15u : run.x == 2 ? 24u : 9u) + 5u + (front ? 0u : 3u);
                         cn.add(K_FLOPS_WRITTEN, hc);
                         if (shadow_needed < 0) cn.add(K_FLOPS_MIN, hc);
                         found = true;
                     }
+                }
+            }
+        }
+        return best >= 0 ? closest : -1.0f;
+    }
+
+    // ---- production scan: same result as scan_closest(ro, rd, 0.001, t_max), fewer instructions ----------
+    // Bit-exact shortcuts (DESIGN.md "Scan"), each guarded so that every input takes either the shortcut
+    // or the as-written code above:
+    //  * fused accept: a test's own range check and hit_scene's `t > 0 && t < closest` (:279) collapse
+    //    into one condition per primitive type (t_min = 0.001 > 0 at every call site, :400,:445);
+    //  * axis-aligned planes (normal = +-unit axis, found at upload): dot(n, d) == +-d_axis and
+    //    dot(p - o, n) == +-(p_axis - o_axis) exactly for finite rays, so t = (p_a - o_a) / d_a;
+    //  * two adjacent parallel axis-aligned planes ("slab pair", the walls of a box): one division for both;
+    //  * triangles: u = (1/a) * dot(s, h) is clearly < 0 or > 1 from the signs / magnitudes of dot(s, h)
+    //    and a (margins cover the two roundings); only the survivors pay 1/a.
+    __device__ __noinline__ float scan_as_written(float3 ro, float3 rd, float t_max, int &best) {
+        return scan_closest(ro, rd, 0.001f, t_max, best, -1);
+    }
+
+    __device__ __forceinline__ float scan_lean(float3 ro, float3 rd, float t_max, int &best) {
+        const float t_min = 0.001f;
+        // non-finite rays (never produced by a sane scene) take the as-written code: 0 * inf is NaN there
+        // (origins beyond 1e30 too: there p - o could overflow; x * 1e8 overflows to inf first)
+        float fin = __fmaf_rn(ro.x * 1e8f, 0.0f, 0.0f);
+        fin = __fmaf_rn(ro.y * 1e8f, 0.0f, fin); fin = __fmaf_rn(ro.z * 1e8f, 0.0f, fin);
+        fin = __fmaf_rn(rd.x, 0.0f, fin); fin = __fmaf_rn(rd.y, 0.0f, fin); fin = __fmaf_rn(rd.z, 0.0f, fin);
+        if (!(fin == 0.0f)) return scan_as_written(ro, rd, t_max, best);
+        float closest = t_max;
+        best = -1;
+        for (int r = 0; r < sc.n_runs; r++) {
+            const int4 run = src.run(r);
+            if (run.x == 0) {                                   // spheres: as written, accept == (t > 0)
+#pragma unroll 1
+                for (int i = run.y; i < run.z; i++) {
+                    uint32_t cost;
+                    const float t = test_sphere(ro, rd, src.ga(i), src.gb(i).x, t_min, closest, cost);
+                    if (t > 0.0f) { closest = t; best = i; }
+                }
+            } else if (run.x >= 6 && run.x <= 8) {              // slab pairs: two parallel axis-aligned planes
+                // Of two planes p_lo < p_hi on one axis a ray can only hit the first one past its origin:
+                // d > 0: the smallest p above o; d < 0: the largest p below o.  The other plane has a larger
+                // t (or t <= 0), so as written it either loses to this one or is rejected: one division
+                // per pair.  Exceptions take the as-written scan: 0 < t < t_min on the chosen plane (the
+                // other one may then be the hit) and |num| so large that both quotients could round alike.
+                const float o_a = run.x == 6 ? ro.x : run.x == 7 ? ro.y : ro.z;
+                const float d_a = run.x == 6 ? rd.x : run.x == 7 ? rd.y : rd.z;
+                const bool live = fabsf(d_a) >= 0.0001f;        //  abs(denom) < 0.0001 -> miss (:180)
+#pragma unroll 1
+                for (int i = run.y; i < run.z; i += 2) {
+                    const float4 pr = src.gc(i);                // (p_lo, p_hi, 1 if the first plane is p_hi, 2^20 * gap)
+                    const bool take_hi = d_a > 0.0f ? !(o_a < pr.x) : (o_a > pr.y);
+                    const float num = (take_hi ? pr.y : pr.x) - o_a;
+                    const float t = num / d_a;
+                    if (live) {
+                        if ((t > 0.0f && t < t_min) || !(fabsf(num) < pr.w)) return scan_as_written(ro, rd, t_max, best);
+                        if (t >= t_min && t < closest) { closest = t; best = i + ((take_hi ? 1 : 0) ^ __float2int_rz(pr.z)); }
+                    }
+                }
+            } else if (run.x >= 3 && run.x <= 5) {              // single axis-aligned planes
+                const float o_a = run.x == 3 ? ro.x : run.x == 4 ? ro.y : ro.z;
+                const float d_a = run.x == 3 ? rd.x : run.x == 4 ? rd.y : rd.z;
+                const bool live = fabsf(d_a) >= 0.0001f;
+#pragma unroll 1
+                for (int i = run.y; i < run.z; i++) {
+                    const float t = (src.ga_axis(i, run.x - 3) - o_a) / d_a;
+                    if (live && t >= t_min && t < closest) { closest = t; best = i; }
+                }
+            } else if (run.x == 1) {                            // general planes: as written, fused accept
+#pragma unroll 1
+                for (int i = run.y; i < run.z; i++) {
+                    const float4 n = src.gb(i);
+                    const float denom = V::dot(xyz(n), rd);
+                    const float t = V::dot(V::sub(xyz(src.ga(i)), ro), xyz(n)) / denom;
+                    if (fabsf(denom) >= 0.0001f && t >= t_min && t < closest) { closest = t; best = i; }
+                }
+            } else if (run.x == 2) {                            // triangles
+#pragma unroll 1
+                for (int i = run.y; i < run.z; i++) {
+                    const float3 e1 = xyz(src.gb(i)), e2 = xyz(src.gc(i));
+                    const float3 h = V::cross(rd, e2);
+                    const float a = V::dot(e1, h);
+                    if (a > -0.00001f && a < 0.00001f) continue;
+                    const float3 s = V::sub(ro, xyz(src.ga(i)));
+                    const float du = V::dot(s, h);
+                    const float aa = fabsf(a), adu = fabsf(du);
+                    // u = RN(RN(1/a) * du): negative (and not flushed to zero) or above 1 beyond the rounding margin
+                    const bool opposite = (__float_as_int(du) ^ __float_as_int(a)) < 0;
+                    if ((opposite && adu > 1e-30f && aa < 1e6f) || adu > aa * 1.000001f) continue;
+                    const float f = 1.0f / a;
+                    const float u = f * du;
+                    if (u < 0.0f || u > 1.0f) continue;
+                    const float3 q = V::cross(s, e1);
+                    const float v = f * V::dot(rd, q);
+                    if (v < 0.0f || u + v > 1.0f) continue;
+                    const float t = f * V::dot(e2, q);
+                    if (t > t_min && t < closest) { closest = t; best = i; }
                 }
             }
         }
@@ -209,7 +308,7 @@ struct Tracer {
             float4 a = __ldg(&sc.ga[i]);
             return V::normalize(V::divs(V::sub(p, xyz(a)), a.w));
         }
-        if (type == 1 || type == 2) return xyz(__ldg(&sc.gn[i]));
+        if (type >= 1 && type <= 8) return xyz(__ldg(&sc.gn[i]));
         return f3(0.0f, 1.0f, 0.0f);
     }
 
@@ -231,8 +330,9 @@ struct Tracer {
         sincos_pinned(phi, sp, cp);
         float x = sin_theta * cp, y = sin_theta * sp, z = cos_theta;
         float3 w = V::normalize(normal);
-        float3 u = (fabsf(w.x) > 0.1f) ? V::normalize(V::cross(f3(0.0f, 1.0f, 0.0f), w))
-                                       : V::normalize(V::cross(f3(1.0f, 0.0f, 0.0f), w));
+        // one cross + normalize for both helper axes (:327-331): same operations, no divergent branch
+        const bool use_y = fabsf(w.x) > 0.1f;
+        float3 u = V::normalize(V::cross(f3(use_y ? 0.0f : 1.0f, use_y ? 1.0f : 0.0f, 0.0f), w));
         float3 v = V::cross(w, u);
         return V::normalize(V::lin3(u, x, v, y, w, z));
     }

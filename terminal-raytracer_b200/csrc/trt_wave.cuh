@@ -95,7 +95,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         // ---- the scan slot: hit_scene for this lane's ray (closest-hit or shadow alike) -------------------
         int best = -1;
         float t_hit = -1.0f;
-        if (mode != WM_DONE && fp.max_depth != 0u) t_hit = tr.scan_closest(ro, rd, 0.001f, t_max, best, -1);
+        if (mode != WM_DONE && fp.max_depth != 0u) t_hit = tr.scan_lean(ro, rd, t_max, best);
 
         __syncwarp();
         bool path_end = false;
@@ -158,10 +158,19 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     light_normal = xyz(nl);
                 }
                 const float3 light_vec = V::sub(light_point, hp);
-                const float light_distance = V::length(light_vec);
-                const float3 light_dir = V::divs(light_vec, light_distance);
-                const float cos_surface = fmaxf(0.0f, V::dot(hn, light_dir));
-                const float cos_light = fmaxf(0.0f, V::dot(light_normal, V::scale(light_dir, -1.0f)));
+                // Early out, exact: if dot(n_light, light_vec) is positive (or dot(n_surface, light_vec)
+                // negative) by more than the rounding of the normalisation that follows, the matching
+                // cosine (:403-404) is certainly 0 and this light adds nothing (DESIGN.md "Light loop").
+                const float d2 = V::dot(light_vec, light_vec);
+                const float sl = V::dot(light_normal, light_vec), ss = V::dot(hn, light_vec);
+                float cos_surface = 0.0f, cos_light = 0.0f, light_distance = 0.0f;
+                float3 light_dir = f3(0.0f, 0.0f, 0.0f);
+                if (!((sl > 0.0f && sl * sl > 1e-11f * d2) || (ss < 0.0f && ss * ss > 1e-11f * d2))) {
+                    light_distance = sqrtf(d2);
+                    light_dir = V::divs(light_vec, light_distance);
+                    cos_surface = fmaxf(0.0f, V::dot(hn, light_dir));
+                    cos_light = fmaxf(0.0f, V::dot(light_normal, V::scale(light_dir, -1.0f)));
+                }
                 if (cos_surface > 0.0f && cos_light > 0.0f) {
                     // contribution if unoccluded (:408-427); the shadow ray goes to the next scan (:399-400)
                     const float geometric = (cos_surface * cos_light) / (light_distance * light_distance);
