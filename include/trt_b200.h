@@ -173,6 +173,9 @@ int trt_device_buffer(trt_ctx *ctx, int which, void **dptr, size_t *bytes);
 int trt_cuda_stream(trt_ctx *ctx, void **stream);
 /* rows this shard owns, ascending; returns the count (writes at most cap entries) */
 uint32_t trt_shard_rows(const trt_ctx *ctx, uint32_t height, uint32_t *rows, uint32_t cap);
+/* the same rule without a context (host-side planning, tests) */
+uint32_t trt_shard_rows_of(uint32_t shard_index, uint32_t shard_count, uint32_t stripe_rows, uint32_t height,
+                           uint32_t *rows, uint32_t cap);
 /* pack this shard's pixel rows contiguously (local row order) into d_dst (device, float4) */
 int trt_pack_shard_pixels(trt_ctx *ctx, void *d_dst, size_t dst_bytes);
 /* quantise a frame assembled from per-shard packed blocks: block r holds shard r's rows, blocks

@@ -120,6 +120,7 @@ SYMBOLS = {
     "trt_device_buffer": (C.c_int, [_P, C.c_int, C.POINTER(_P), C.POINTER(C.c_size_t)]),
     "trt_cuda_stream": (C.c_int, [_P, C.POINTER(_P)]),
     "trt_shard_rows": (C.c_uint32, [_P, C.c_uint32, _P, C.c_uint32]),
+    "trt_shard_rows_of": (C.c_uint32, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _P, C.c_uint32]),
     "trt_pack_shard_pixels": (C.c_int, [_P, _P, C.c_size_t]),
     "trt_quantise_gathered": (C.c_int, [_P, _P, C.c_size_t, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                         C.POINTER(C.c_size_t)]),
@@ -389,6 +390,12 @@ class Renderer:
                                              mode, C.byref(n) if want_len else None))
         self.size = (width, height)
         return n.value
+
+
+def shard_rows_of(shard_index, shard_count, stripe_rows, height) -> np.ndarray:
+    rows = np.zeros(max(1, height), np.uint32)
+    n = lib().trt_shard_rows_of(shard_index, shard_count, stripe_rows, height, rows.ctypes.data, height)
+    return rows[:n]
 
 
 def selftest_div3(n_cases, seed=1, distribution=0, device=0):

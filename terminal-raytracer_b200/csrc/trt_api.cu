@@ -279,6 +279,18 @@ static void shard_rows(const trt_config &c, uint32_t h, std::vector<uint32_t> &r
     }
 }
 
+extern "C" uint32_t trt_shard_rows_of(uint32_t shard_index, uint32_t shard_count, uint32_t stripe_rows, uint32_t height,
+                                      uint32_t *rows, uint32_t cap) {
+    trt_config c{};
+    c.shard_index = shard_index;
+    c.shard_count = shard_count ? shard_count : 1u;
+    c.stripe_rows = stripe_rows ? stripe_rows : 1u;
+    std::vector<uint32_t> r;
+    shard_rows(c, height, r);
+    for (uint32_t i = 0; i < r.size() && i < cap && rows; i++) rows[i] = r[i];
+    return (uint32_t)r.size();
+}
+
 extern "C" uint32_t trt_shard_rows(const trt_ctx *ctx, uint32_t height, uint32_t *rows, uint32_t cap) {
     if (!ctx) return 0;
     std::vector<uint32_t> r;
