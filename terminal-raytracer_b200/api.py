@@ -332,6 +332,12 @@ class Renderer:
         self._ck(lib().trt_read_stream(self.h, p, cap, C.byref(n)))
         return C.string_at(p, n.value)
 
+    def read_stream_into(self, host_ptr, cap) -> int:
+        """Copy the last quantised stream into the caller's (pinned) buffer; returns its length."""
+        n = C.c_size_t()
+        self._ck(lib().trt_read_stream(self.h, host_ptr, cap, C.byref(n)))
+        return n.value
+
     def _read(self, fn, dtype, cols):
         w, h = self.size
         a = np.zeros((w * h, cols), dtype) if cols else np.zeros(w * h, dtype)
