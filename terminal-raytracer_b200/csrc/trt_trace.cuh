@@ -27,6 +27,7 @@ struct ConstScene {
 __constant__ ConstScene c_scene;
 
 struct SrcGlobal {
+    static constexpr int kUnroll = 4;       // HBM/L2 latency: keep several primitives' loads in flight
     const SceneView &sc;
     const LightView &lv;
     __device__ SrcGlobal(const SceneView &s, const LightView &l) : sc(s), lv(l) {}
@@ -42,6 +43,7 @@ struct SrcGlobal {
     __device__ __forceinline__ float4 le(int k) const { return __ldg(&lv.le[k]); }
 };
 struct SrcConst {
+    static constexpr int kUnroll = 1;       // constant bank: no load latency; keep the loop body small (I-cache)
     const SceneView &sc;
     __device__ SrcConst(const SceneView &s, const LightView &) : sc(s) {}
     __device__ __forceinline__ float4 ga(int i) const { return c_scene.ga[i]; }
@@ -215,7 +217,7 @@ struct Tracer {
         for (int r = 0; r < sc.n_runs; r++) {
             const int4 run = src.run(r);
             if (run.x == 0) {                                   // spheres: as written, accept == (t > 0)
-#pragma unroll 1
+#pragma unroll SRC::kUnroll
                 for (int i = run.y; i < run.z; i++) {
                     uint32_t cost;
                     const float t = test_sphere(ro, rd, src.ga(i), src.gb(i).x, t_min, closest, cost);
@@ -230,7 +232,7 @@ struct Tracer {
                 const float o_a = run.x == 6 ? ro.x : run.x == 7 ? ro.y : ro.z;
                 const float d_a = run.x == 6 ? rd.x : run.x == 7 ? rd.y : rd.z;
                 const bool live = fabsf(d_a) >= 0.0001f;        //  abs(denom) < 0.0001 -> miss (:180)
-#pragma unroll 1
+#pragma unroll SRC::kUnroll
                 for (int i = run.y; i < run.z; i += 2) {
                     const float4 pr = src.gc(i);                // (p_lo, p_hi, 1 if the first plane is p_hi, 2^20 * gap)
                     const bool take_hi = d_a > 0.0f ? !(o_a < pr.x) : (o_a > pr.y);
@@ -245,13 +247,13 @@ struct Tracer {
                 const float o_a = run.x == 3 ? ro.x : run.x == 4 ? ro.y : ro.z;
                 const float d_a = run.x == 3 ? rd.x : run.x == 4 ? rd.y : rd.z;
                 const bool live = fabsf(d_a) >= 0.0001f;
-#pragma unroll 1
+#pragma unroll SRC::kUnroll
                 for (int i = run.y; i < run.z; i++) {
                     const float t = (src.ga_axis(i, run.x - 3) - o_a) / d_a;
                     if (live && t >= t_min && t < closest) { closest = t; best = i; }
                 }
             } else if (run.x == 1) {                            // general planes: as written, fused accept
-#pragma unroll 1
+#pragma unroll SRC::kUnroll
                 for (int i = run.y; i < run.z; i++) {
                     const float4 n = src.gb(i);
                     const float denom = V::dot(xyz(n), rd);
@@ -259,7 +261,7 @@ struct Tracer {
                     if (fabsf(denom) >= 0.0001f && t >= t_min && t < closest) { closest = t; best = i; }
                 }
             } else if (run.x == 2) {                            // triangles
-#pragma unroll 1
+#pragma unroll SRC::kUnroll
                 for (int i = run.y; i < run.z; i++) {
                     const float3 e1 = xyz(src.gb(i)), e2 = xyz(src.gc(i));
                     const float3 h = V::cross(rd, e2);

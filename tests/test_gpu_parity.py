@@ -153,3 +153,63 @@ def test_row_shards_union_equals_whole(pkg, O):
         r.close()
     assert seen.all()
     assert np.array_equal(_bits(union), _bits(ref))
+
+
+@pytest.mark.parametrize("conv", [0, 1])
+def test_large_scene_global_memory_path(pkg, O, conv):
+    """> 256 primitives: geometry comes from the SoA arrays in HBM, not from __constant__ memory.
+    A reduced C4 (BASELINE.json configs[3]): random spheres + triangles + 2 emissive quads, NEE live."""
+    sc = O.make_c4_scene(n_spheres=150, n_tris=400, width=64, height=36, spp=16, max_depth=6)
+    prims = O.flatten_scene(sc)
+    assert len(prims) > 256
+    u = O.make_uniforms(sc, len(prims), O.C4_SEED, 0)
+    ref = O.render(prims, u, conv=conv, want_counters=True)
+    r = pkg.Renderer(64, 36, conv=conv)
+    r.upload_scene(prims)
+    stream = r.render_frame(_u(pkg, u), pkg.MODE_ASCII)
+    got = r.read_pixels()
+    r.close()
+    bad = int((_bits(got) != _bits(ref["pixels"])).any(axis=1).sum())
+    assert bad == 0, f"{bad} pixels differ"
+    assert stream == O.quantise(got, 64, 36, 0)[0]
+    rc = pkg.Renderer(64, 36, conv=conv, count_work=True)
+    rc.upload_scene(prims)
+    rc.render_frame(_u(pkg, u), pkg.MODE_NONE)
+    assert rc.counters() == ref["counters"]
+    rc.close()
+
+
+def test_mixed_plane_kinds_and_run_order(pkg, O):
+    """Scan-order corner cases for the production scan: tilted planes, single axis-aligned planes,
+    slab pairs in both orders, coincident planes, a ray origin within t_min of a wall, unknown types."""
+    sc = {"width": 72, "height": 40, "samples_per_pixel": 16, "max_depth": 8, "frames_to_accumulate": 1,
+          "camera": {"fov_degrees": 60.0, "char_aspect_ratio": 0.55},
+          "spheres": [{"center": [0.3, -0.2, -2.0], "radius": 0.5, "color": [0.9, 0.5, 0.5], "emission": [0, 0, 0], "reflectivity": 0.4},
+                      {"center": [-0.8, 0.6, -2.6], "radius": 0.3, "color": [1, 1, 1], "emission": [6, 6, 6], "reflectivity": 0.0}],
+          "planes": [
+              {"point": [0, 1.5, 0], "normal": [0, -1, 0], "color": [0.8, 0.8, 0.8], "emission": [0, 0, 0], "reflectivity": 0.0},   # pair (hi first)
+              {"point": [0, -1.0, 0], "normal": [0, 1, 0], "color": [0.7, 0.7, 0.9], "emission": [0, 0, 0], "reflectivity": 0.2},
+              {"point": [0, -1.0005, 0], "normal": [0, 1, 0], "color": [0.1, 0.9, 0.1], "emission": [0, 0, 0], "reflectivity": 0.0},  # single, 0.5 mm below the floor
+              {"point": [0, 0, -4], "normal": [0.2, 0.1, 1.0], "color": [0.9, 0.9, 0.3], "emission": [0, 0, 0], "reflectivity": 0.0},  # tilted, un-normalised
+              {"point": [-2, 0, 0], "normal": [1, 0, 0], "color": [0.9, 0.3, 0.3], "emission": [0, 0, 0], "reflectivity": 0.0},      # pair (lo first)
+              {"point": [2, 0, 0], "normal": [-1, 0, 0], "color": [0.3, 0.3, 0.9], "emission": [0, 0, 0], "reflectivity": 0.6},
+              {"point": [0, 0, 1], "normal": [0, 0, -2], "color": [0.5, 0.5, 0.5], "emission": [0, 0, 0], "reflectivity": 0.0},      # axis direction but |n| = 2: general plane
+              {"point": [0, 0, 3], "normal": [0, 0, -1], "color": [0.5, 0.5, 0.5], "emission": [0, 0, 0], "reflectivity": 0.0},      # coincident pair -> not paired
+              {"point": [0, 0, 3], "normal": [0, 0, -1], "color": [0.9, 0.1, 0.9], "emission": [0, 0, 0], "reflectivity": 0.0}],
+          "triangles": [{"v0": [-1, 1.49, -3], "v1": [1, 1.49, -3], "v2": [0, 1.49, -1.5], "color": [1, 1, 1], "emission": [9, 9, 9], "reflectivity": 0.0},
+                        {"v0": [-1.5, -1, -3.5], "v1": [-0.5, -1, -3.5], "v2": [-1, 0.5, -3.2], "color": [0.2, 0.8, 0.8], "emission": [0, 0, 0], "reflectivity": 0.3}]}
+    prims = O.flatten_scene(sc)
+    weird = prims.copy()
+    weird = np.concatenate([weird[:3], weird[2:3], weird[3:]])      # an unknown-type record in the middle of the scan order
+    weird[3]["type"] = 7
+    for P in (prims, weird):
+        for conv in (0, 1):
+            u = O.make_uniforms(sc, len(P), 21, 0)
+            ref = O.render(P, u, conv=conv)
+            r = pkg.Renderer(72, 40, conv=conv)
+            r.upload_scene(P)
+            r.render_frame(_u(pkg, u), pkg.MODE_NONE)
+            got = r.read_pixels()
+            r.close()
+            bad = int((_bits(got) != _bits(ref["pixels"])).any(axis=1).sum())
+            assert bad == 0, f"conv {conv}: {bad} pixels differ"

@@ -1,0 +1,43 @@
+"""BASELINE.json configs[4] (C5): 600-frame scripted camera path on scene2.json as shipped (200x100, 32 spp,
+depth 4), one key per frame `w,Right,d,Up,s,Left,a,Down` repeating (lib.rs:392-405), accumulation reset
+on every move (frame_number = 0), seed_i = C1_SEED + 0x9E3779B9*i, ASCII.  Reports p50 / p99 of the wall
+latency of trt_render_frame (uniforms in -> bytes in host memory), and checks a few frames against the oracle."""
+import json, os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import __graft_entry__ as g
+pkg, O = g.load_package(), g.load_oracle()
+frames = int(sys.argv[1]) if len(sys.argv) > 1 else 600
+scene = pkg.Scene.parse(json.dumps(O.SCENE2))
+cam, ocam = pkg.Camera(), O.Camera()
+info = scene.info
+r = pkg.Renderer(info.width, info.height)
+r.upload_scene(scene)
+oprims = O.flatten_scene(O.SCENE2)
+lat, checked, nbytes = [], 0, 0
+for i in range(-20, frames):                       # 20 untimed warm-up frames
+    k = O.C5_KEYS[i % 8]
+    moved = cam.key(k)
+    u = scene.uniforms(cam, O.c2_seed(max(i, 0)), 0 if moved else 1)
+    t0 = time.perf_counter()
+    stream = r.render_frame(u, pkg.MODE_ASCII)
+    dt = time.perf_counter() - t0
+    if i >= 0:
+        lat.append(dt * 1e3); nbytes += len(stream)
+        ocam.key(k)
+        if i % 150 == 0:                            # parity spot checks against the oracle
+            ou = O.make_uniforms(O.SCENE2, len(oprims), O.c2_seed(i), 0, camera=ocam)
+            assert bytes(u) == ou.tobytes()
+            ref = O.render(oprims, ou)
+            assert np.array_equal(r.read_pixels().view(np.uint32), ref["pixels"].view(np.uint32))
+            assert stream == O.quantise(ref["pixels"], info.width, info.height, 0)[0]
+            checked += 1
+    else:
+        ocam.key(k)
+lat = np.array(lat)
+t = r.timings()
+print(json.dumps({"config": "C5 scene2.json 200x100 32spp depth4, 600 scripted keys, reset per move, ASCII",
+                  "frames": frames, "p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)),
+                  "mean_ms": float(lat.mean()), "max_ms": float(lat.max()), "fps": 1e3 / float(lat.mean()),
+                  "bytes_per_frame": nbytes // frames, "last_frame_device_ms": {"trace": t.trace_ms, "quantise": t.quantise_ms, "d2h": t.d2h_ms},
+                  "oracle_checked_frames": checked}))
