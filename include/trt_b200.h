@@ -83,6 +83,9 @@ typedef struct trt_ctx trt_ctx;
 /* arithmetic convention of the trace kernel (DESIGN.md "Arithmetic conventions") */
 #define TRT_CONV_AS_WRITTEN 0     /* one IEEE rounding per WGSL operator, no contraction */
 #define TRT_CONV_FUSED      1     /* fused multiply-add inside the vector helpers        */
+#define TRT_CONV_NATIVE     2     /* what a GPU shader compiler gives the same WGSL: FFMA contraction and the SM's
+                                     reciprocal / rsqrt / sqrt / sin / cos units (1-2 ulp, inside WGSL's accuracy
+                                     bounds); tracks conv 0 to rounding noise, not bit for bit */
 
 /* output mode of the quantiser: lib.rs:509-513 (truecolor) / lib.rs:515-524 (ASCII) */
 #define TRT_MODE_ASCII      0

@@ -8,4 +8,4 @@ include/trt_b200.h); `api` is its ctypes face and `multigpu` the torch.distribut
 """
 from . import api  # noqa: F401
 from .api import (Camera, Renderer, Scene, TrtError, Uniforms, run,  # noqa: F401
-                  CONV_AS_WRITTEN, CONV_FUSED, MODE_ASCII, MODE_TRUECOLOR, MODE_NONE)
+                  CONV_AS_WRITTEN, CONV_FUSED, CONV_NATIVE, MODE_ASCII, MODE_TRUECOLOR, MODE_NONE)

@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TRT_B200_LIB") or os.path.join(HERE, "libtrt_b200.so")
 
 TRT_ABI_VERSION = 1
-CONV_AS_WRITTEN, CONV_FUSED = 0, 1
+CONV_AS_WRITTEN, CONV_FUSED, CONV_NATIVE = 0, 1, 2
 MODE_ASCII, MODE_TRUECOLOR, MODE_NONE = 0, 1, 2
 KEY_UP, KEY_DOWN, KEY_LEFT, KEY_RIGHT = 1001, 1002, 1003, 1004
 KEYS = {"w": ord("w"), "a": ord("a"), "s": ord("s"), "d": ord("d"),

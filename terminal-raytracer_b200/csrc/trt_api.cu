@@ -14,6 +14,13 @@
 
 using namespace trt;
 
+// conv 2 lives in its own translation unit (trt_native.cu: --fmad=true -use_fast_math)
+namespace trt {
+cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
+                                const LightView &lv, const FrameParams &fp, int sm_count, cudaStream_t stream,
+                                uint32_t *launches);
+}
+
 struct trt_ctx {
     trt_config cfg{};
     int device = 0;
@@ -102,7 +109,7 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
     *out = nullptr;
     if (cfg->abi_version != TRT_ABI_VERSION) return fail(nullptr, TRT_ERR_INVALID, "trt_create: ABI version mismatch");
     if (cfg->max_width == 0 || cfg->max_height == 0) return fail(nullptr, TRT_ERR_INVALID, "trt_create: zero frame size");
-    if (cfg->conv > 1u) return fail(nullptr, TRT_ERR_INVALID, "trt_create: unknown arithmetic convention");
+    if (cfg->conv > 2u) return fail(nullptr, TRT_ERR_INVALID, "trt_create: unknown arithmetic convention");
     if (cfg->shard_count > 1u && cfg->shard_index >= cfg->shard_count)
         return fail(nullptr, TRT_ERR_INVALID, "trt_create: shard_index >= shard_count");
     int n_dev = 0;
@@ -252,7 +259,8 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     rp.le = ctx->d_lgeom + 4 * cl;
     const uint32_t work = count > n_lights ? count : n_lights;
     if (work) {
-        if (ctx->cfg.conv) repack_kernel<1><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
+        // conv 2 keeps the as-written derived values (unit normals, edges, r^2): only the per-ray math is native
+        if (ctx->cfg.conv == 1u) repack_kernel<1><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
         else repack_kernel<0><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
         CK(cudaGetLastError());
     }
@@ -360,9 +368,14 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     if (fp.n_local_pixels) {
         if (ctx->cfg.count_work) {
             const uint32_t blocks = (fp.n_local_pixels + 127u) / 128u;
-            if (ctx->cfg.conv) trace_pixel_kernel<1, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
+            // the work counters are those of the as-written shader: conv 2 contexts count with conv 0 arithmetic
+            if (ctx->cfg.conv == 1u) trace_pixel_kernel<1, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
             else trace_pixel_kernel<0, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
             ctx->launches += 1;
+        } else if (ctx->cfg.conv == 2u) {
+            cudaError_t e = native_trace_launch(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, fp, ctx->sm_count,
+                                                ctx->stream, &ctx->launches);
+            if (e != cudaSuccess) { ctx->err = std::string("native trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
         } else {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
             // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)

@@ -58,7 +58,7 @@ __device__ __forceinline__ float3 xyz(float4 v) { return make_float3(v.x, v.y, v
 // which is RN(a/s) whenever a, s and a/s are normal numbers away from the exponent limits, and keeps
 // the signed zero of a zero numerator (q0).  Anything else (tiny, huge, infinite, NaN) goes to the
 // plain IEEE division in div3_slow.  tests/test_gpu_division.py checks it against `/` bit for bit.
-__device__ __noinline__ float3 div3_slow(float ax, float ay, float az, float s) { return make_float3(ax / s, ay / s, az / s); }
+static __device__ __noinline__ float3 div3_slow(float ax, float ay, float az, float s) { return make_float3(ax / s, ay / s, az / s); }
 
 __device__ __forceinline__ float3 div3_rn(float3 a, float s) {
     float y;
@@ -82,13 +82,27 @@ __device__ __forceinline__ float3 div3_rn(float3 a, float s) {
     return make_float3(ox, oy, oz);
 }
 
+// ---- conv 2 "device native": the arithmetic a GPU shader compiler gives the same WGSL --------------
+// WGSL only bounds the error of `/` (2.5 ulp), sqrt / inverseSqrt (2 ulp), sin / cos (2^-11 absolute)
+// and allows fused multiply-add everywhere; conv 2 uses the SM's native units within those bounds:
+// MUFU.RCP / RSQ / SQRT / SIN / COS (1-2 ulp) and FFMA contraction (this convention is only
+// instantiated in trt_native.cu, which is compiled with --fmad=true -use_fast_math).
+__device__ __forceinline__ float rcp_native(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rsqrt_native(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sqrt_native(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
 // ---- vector helpers (shader.wgsl:83-101,126-140,225-232) ----------------------------------------
 template <int CONV> struct M {
     static __device__ __forceinline__ float3 add(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
     static __device__ __forceinline__ float3 sub(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
     static __device__ __forceinline__ float3 scale(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
     static __device__ __forceinline__ float3 mulv(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
-    static __device__ __forceinline__ float3 divs(float3 a, float s) { return div3_rn(a, s); }     // == a.x/s, a.y/s, a.z/s
+    static __device__ __forceinline__ float3 divs(float3 a, float s) {                              // == a.x/s, a.y/s, a.z/s
+        if (CONV == 2) { const float y = rcp_native(s); return f3(a.x * y, a.y * y, a.z * y); }
+        return div3_rn(a, s);
+    }
+    static __device__ __forceinline__ float div(float a, float b) { return CONV == 2 ? a * rcp_native(b) : a / b; }
+    static __device__ __forceinline__ float sqrt(float a) { return CONV == 2 ? sqrt_native(a) : sqrtf(a); }
     static __device__ __forceinline__ float dot(float3 a, float3 b) {
         if (CONV) return __fmaf_rn(a.z, b.z, __fmaf_rn(a.y, b.y, a.x * b.x));
         return a.x * b.x + a.y * b.y + a.z * b.z;
@@ -111,8 +125,11 @@ template <int CONV> struct M {
                       __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
         return f3(a.x * s + b.x * t + c.x * u, a.y * s + b.y * t + c.y * u, a.z * s + b.z * t + c.z * u);
     }
-    static __device__ __forceinline__ float length(float3 v) { return sqrtf(dot(v, v)); }
-    static __device__ __forceinline__ float3 normalize(float3 v) { return divs(v, length(v)); }
+    static __device__ __forceinline__ float length(float3 v) { return sqrt(dot(v, v)); }
+    static __device__ __forceinline__ float3 normalize(float3 v) {
+        if (CONV == 2) { const float y = rsqrt_native(dot(v, v)); return f3(v.x * y, v.y * y, v.z * y); }
+        return divs(v, length(v));
+    }
     static __device__ __forceinline__ float3 reflect(float3 v, float3 n) {                 // shader.wgsl:138-140
         float k = 2.0f * dot(v, n);
         if (CONV) return f3(__fmaf_rn(n.x, -k, v.x), __fmaf_rn(n.y, -k, v.y), __fmaf_rn(n.z, -k, v.z));
@@ -162,6 +179,17 @@ __device__ __forceinline__ void sincos_pinned(float phi, float &sn, float &cs) {
     if (k >= 2) so = -so;
     sn = so;
     cs = co;
+}
+
+// conv 2: MUFU.SIN / MUFU.COS on the angle folded into (-pi, pi] (their best range); r2 in [0, 1]
+template <int CONV> __device__ __forceinline__ void sincos_turn(float r2, float &sn, float &cs) {
+    if (CONV == 2) {
+        const float phi = 6.28318530718f * (r2 > 0.5f ? r2 - 1.0f : r2);
+        sn = __sinf(phi);
+        cs = __cosf(phi);
+    } else {
+        sincos_pinned(6.28318530718f * r2, sn, cs);
+    }
 }
 
 #define TRT_PI_F 3.14159265359f

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(128) trace_pixel_kernel(SceneView sc, LightVie
 }
 
 // pack the rows this shard owns contiguously (local row order) for the NCCL gather
-__global__ void pack_rows_kernel(const float4 *src, float4 *dst, const uint32_t *row_map, uint32_t width,
+static __global__ void pack_rows_kernel(const float4 *src, float4 *dst, const uint32_t *row_map, uint32_t width,
                                  uint32_t n_local_pixels) {
     const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
     if (lp < n_local_pixels) {

@@ -1,0 +1,33 @@
+// trt_native.cu -- the trace kernel in the "device native" arithmetic convention (conv 2).
+//
+// Same kernel source as the strict build (trt_wave.cuh: same state machine, same random-number
+// order, same tests in the same scan order); what differs is the arithmetic: this translation unit
+// is compiled with --fmad=true -use_fast_math, so a*b+c contracts to FFMA and `/`, sqrt, sin, cos
+// map to the SM's MUFU units (1-2 ulp) -- exactly the latitude WGSL gives the reference's own shader
+// compiler (naga -> driver; DESIGN.md "Arithmetic conventions").  Results track the strict build to
+// rounding noise; the tolerance tests (tests/test_gpu_native.py) state the bounds.
+#define TRT_NATIVE_TU 1
+#include "trt_kernels.cuh"
+#include "trt_persistent.cuh"
+#include "trt_wave.cuh"
+
+namespace trt {
+
+cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
+                                const LightView &lv, const FrameParams &fp, int sm_count, cudaStream_t stream,
+                                uint32_t *launches) {
+    // this translation unit has its own __constant__ mirror of the scene
+    cudaError_t e = persistent_bind_scene(device, ctx_key, serial, sv, lv, stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    const uint32_t want = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
+    const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
+    const uint32_t blocks = want < cap ? want : cap;
+    if (scene_fits_constant(sv)) trace_wave_kernel<2, SrcConst><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+    else trace_wave_kernel<2, SrcGlobal><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+    *launches += 1;
+    return cudaGetLastError();
+}
+
+}  // namespace trt

@@ -161,6 +161,7 @@ static inline cudaError_t persistent_bind_scene(int device, const void *ctx_key,
     return e;
 }
 
+#ifndef TRT_NATIVE_TU      // the strict launchers instantiate conv 0 / 1 only in trt_api.cu
 static inline cudaError_t persistent_trace_launch(const SceneView &sv, const LightView &lv, const FrameParams &fp, int conv,
                                                   int sm_count, cudaStream_t stream, uint32_t *launches) {
     cudaError_t e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
@@ -179,5 +180,7 @@ static inline cudaError_t persistent_trace_launch(const SceneView &sv, const Lig
     *launches += 1;
     return cudaGetLastError();
 }
+
+#endif
 
 }  // namespace trt

@@ -24,7 +24,7 @@ struct ConstScene {
     float4 la[TRT_CONST_LIGHTS], lb[TRT_CONST_LIGHTS], lc[TRT_CONST_LIGHTS], ln[TRT_CONST_LIGHTS], le[TRT_CONST_LIGHTS];
     int4 runs[TRT_CONST_RUNS];
 };
-__constant__ ConstScene c_scene;
+static __constant__ ConstScene c_scene;      // one mirror per translation unit (strict / native builds)
 
 struct SrcGlobal {
     static constexpr int kUnroll = 4;       // HBM/L2 latency: keep several primitives' loads in flight
@@ -287,6 +287,82 @@ struct Tracer {
         return best >= 0 ? closest : -1.0f;
     }
 
+    // ---- conv 2 scan: hit_scene (shader.wgsl:248-294) in the device-native convention ---------------------
+    // Same tests, same order, same strict `t < closest` accept (first index wins ties); divisions are
+    // MUFU.RCP products and the compiler contracts.  One reciprocal per ray axis serves every axis-
+    // aligned plane; of a slab pair only the plane ahead of the origin is evaluated (the other one has
+    // t <= 0 or a larger t), except when that plane is closer than t_min: then the second plane is
+    // tested too, as hit_scene would.
+    __device__ __forceinline__ float scan_native(float3 ro, float3 rd, float t_max, int &best) {
+        const float t_min = 0.001f;
+        float closest = t_max;
+        best = -1;
+        const float3 inv = f3(rcp_native(rd.x), rcp_native(rd.y), rcp_native(rd.z));
+        for (int r = 0; r < sc.n_runs; r++) {
+            const int4 run = src.run(r);
+            if (run.x == 0) {
+#pragma unroll SRC::kUnroll
+                for (int i = run.y; i < run.z; i++) {
+                    uint32_t cost;
+                    const float t = test_sphere(ro, rd, src.ga(i), src.gb(i).x, t_min, closest, cost);
+                    if (t > 0.0f) { closest = t; best = i; }
+                }
+            } else if (run.x >= 3 && run.x <= 8) {
+                const int axis = run.x >= 6 ? run.x - 6 : run.x - 3;
+                const float o_a = axis == 0 ? ro.x : axis == 1 ? ro.y : ro.z;
+                const float d_a = axis == 0 ? rd.x : axis == 1 ? rd.y : rd.z;
+                const float i_a = axis == 0 ? inv.x : axis == 1 ? inv.y : inv.z;
+                const bool live = fabsf(d_a) >= 0.0001f;
+                if (run.x >= 6) {
+#pragma unroll SRC::kUnroll
+                    for (int i = run.y; i < run.z; i += 2) {
+                        const float4 pr = src.gc(i);            // (p_lo, p_hi, 1 if the first plane is p_hi, -)
+                        const bool take_hi = d_a > 0.0f ? !(o_a < pr.x) : (o_a > pr.y);
+                        const float t = ((take_hi ? pr.y : pr.x) - o_a) * i_a;
+                        const int first_hi = __float2int_rz(pr.z);
+                        if (live && t >= t_min && t < closest) { closest = t; best = i + ((take_hi ? 1 : 0) ^ first_hi); }
+                        if (live && t > 0.0f && t < t_min) {    // rare: the other plane of the pair may be the hit
+                            const float t2 = ((take_hi ? pr.x : pr.y) - o_a) * i_a;
+                            if (t2 >= t_min && t2 < closest) { closest = t2; best = i + ((take_hi ? 0 : 1) ^ first_hi); }
+                        }
+                    }
+                } else {
+#pragma unroll SRC::kUnroll
+                    for (int i = run.y; i < run.z; i++) {
+                        const float t = (src.ga_axis(i, axis) - o_a) * i_a;
+                        if (live && t >= t_min && t < closest) { closest = t; best = i; }
+                    }
+                }
+            } else if (run.x == 1) {
+#pragma unroll SRC::kUnroll
+                for (int i = run.y; i < run.z; i++) {
+                    const float4 n = src.gb(i);
+                    const float denom = V::dot(xyz(n), rd);
+                    const float t = V::dot(V::sub(xyz(src.ga(i)), ro), xyz(n)) * rcp_native(denom);
+                    if (fabsf(denom) >= 0.0001f && t >= t_min && t < closest) { closest = t; best = i; }
+                }
+            } else if (run.x == 2) {
+#pragma unroll SRC::kUnroll
+                for (int i = run.y; i < run.z; i++) {
+                    const float3 e1 = xyz(src.gb(i)), e2 = xyz(src.gc(i));
+                    const float3 h = V::cross(rd, e2);
+                    const float a = V::dot(e1, h);
+                    if (a > -0.00001f && a < 0.00001f) continue;
+                    const float f = rcp_native(a);
+                    const float3 s = V::sub(ro, xyz(src.ga(i)));
+                    const float u = f * V::dot(s, h);
+                    if (u < 0.0f || u > 1.0f) continue;
+                    const float3 q = V::cross(s, e1);
+                    const float v = f * V::dot(rd, q);
+                    if (v < 0.0f || u + v > 1.0f) continue;
+                    const float t = f * V::dot(e2, q);
+                    if (t > t_min && t < closest) { closest = t; best = i; }
+                }
+            }
+        }
+        return best >= 0 ? closest : -1.0f;
+    }
+
     // any-hit form of the same scan for shadow rays: only `hit.t < 0` is read by the caller
     // (shader.wgsl:400-402), and before the first accepted hit the bound is still t_max, so stopping at
     // the first accepted primitive returns the same truth value.
@@ -327,9 +403,8 @@ struct Tracer {
         if (COUNT) cn.add(K_RNG_DRAWS, 2);
         float cos_theta = sqrtf(r1);
         float sin_theta = sqrtf(1.0f - r1);
-        float phi = TRT_TWO_PI_F * r2;
         float sp, cp;
-        sincos_pinned(phi, sp, cp);
+        sincos_turn<CONV>(r2, sp, cp);                      // phi = 2 pi r2 (:317)
         float x = sin_theta * cp, y = sin_theta * sp, z = cos_theta;
         float3 w = V::normalize(normal);
         // one cross + normalize for both helper axes (:327-331): same operations, no divergent branch
@@ -355,9 +430,8 @@ struct Tracer {
             if (type == 0) {                                   // uniform sphere sampling :352-369
                 float cos_theta = 1.0f - 2.0f * r1;
                 float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-                float phi = TRT_TWO_PI_F * r2;
                 float sp, cp;
-                sincos_pinned(phi, sp, cp);
+                sincos_turn<CONV>(r2, sp, cp);              // phi = 2 pi r2 (:355)
                 float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
                 light_point = V::axpy(xyz(a), local, a.w);
                 light_normal = local;

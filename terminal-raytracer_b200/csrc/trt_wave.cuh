@@ -95,7 +95,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         // ---- the scan slot: hit_scene for this lane's ray (closest-hit or shadow alike) -------------------
         int best = -1;
         float t_hit = -1.0f;
-        if (mode != WM_DONE && fp.max_depth != 0u) t_hit = tr.scan_lean(ro, rd, t_max, best);
+        if (mode != WM_DONE && fp.max_depth != 0u) t_hit = CONV == 2 ? tr.scan_native(ro, rd, t_max, best) : tr.scan_lean(ro, rd, t_max, best);
 
         __syncwarp();
         bool path_end = false;
@@ -146,7 +146,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     const float cos_theta = 1.0f - 2.0f * r1;
                     const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
                     float sp, cp;
-                    sincos_pinned(TRT_TWO_PI_F * r2, sp, cp);
+                    sincos_turn<CONV>(r2, sp, cp);
                     const float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
                     light_point = V::axpy(xyz(a), local, a.w);
                     light_normal = local;
@@ -165,7 +165,13 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                 const float sl = V::dot(light_normal, light_vec), ss = V::dot(hn, light_vec);
                 float cos_surface = 0.0f, cos_light = 0.0f, light_distance = 0.0f;
                 float3 light_dir = f3(0.0f, 0.0f, 0.0f);
-                if (!((sl > 0.0f && sl * sl > 1e-11f * d2) || (ss < 0.0f && ss * ss > 1e-11f * d2))) {
+                if (CONV == 2) {                                  // native: one MUFU.RSQ, no branch
+                    const float inv_len = rsqrt_native(d2);
+                    light_distance = d2 * inv_len;
+                    light_dir = V::scale(light_vec, inv_len);
+                    cos_surface = fmaxf(0.0f, ss * inv_len);
+                    cos_light = fmaxf(0.0f, -(sl * inv_len));
+                } else if (!((sl > 0.0f && sl * sl > 1e-11f * d2) || (ss < 0.0f && ss * ss > 1e-11f * d2))) {
                     light_distance = sqrtf(d2);
                     light_dir = V::divs(light_vec, light_distance);
                     cos_surface = fmaxf(0.0f, V::dot(hn, light_dir));
@@ -245,6 +251,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
     tr.flush_stats();
 }
 
+#ifndef TRT_NATIVE_TU      // the strict launchers instantiate conv 0 / 1 only in trt_api.cu
 static inline cudaError_t wave_trace_launch(const SceneView &sv, const LightView &lv, const FrameParams &fp, int conv,
                                             int sm_count, bool small, cudaStream_t stream, uint32_t *launches) {
     cudaError_t e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
@@ -262,5 +269,7 @@ static inline cudaError_t wave_trace_launch(const SceneView &sv, const LightView
     *launches += 1;
     return cudaGetLastError();
 }
+
+#endif
 
 }  // namespace trt

@@ -9,7 +9,7 @@ rep, ksub = sys.argv[1:3]
 min_pct = float(sys.argv[3]) if len(sys.argv) > 3 else 0.4
 d = tempfile.mkdtemp()
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-subprocess.run(f"cd {d} && cuobjdump -xelf all {root}/terminal-raytracer_b200/libtrt_b200.so >/dev/null && nvdisasm -g -c trt_api.sm_100a.cubin > all.dis 2>&1; ncu -i {os.path.abspath(rep)} --page source --csv 2>/dev/null > src.csv", shell=True)
+subprocess.run(f"cd {d} && cuobjdump -xelf all {root}/terminal-raytracer_b200/libtrt_b200.so >/dev/null && for c in trt_api trt_native; do nvdisasm -g -c $c.sm_100a.cubin; done > all.dis 2>&1; ncu -i {os.path.abspath(rep)} --page source --csv 2>/dev/null > src.csv", shell=True)
 rows = list(csv.reader(open(d + '/src.csv')))
 hi = next(i for i, r in enumerate(rows) if r and r[0] == 'Address'); hdr = rows[hi]; ci = {h: i for i, h in enumerate(hdr)}
 data = [r for r in rows[hi + 1:] if len(r) >= len(hdr) and r[0].startswith('0x')]
