@@ -327,15 +327,35 @@ def ours(args):
         cpu = {"value": s / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": "port",
                "sample": f"{n} of {w * h} pixels on a regular stride ({s} samples, {dt:.1f} s)"}
 
+    # ---- the same frame in the strict convention (conv 0: bit-exact against the oracle), for comparison ----
+    strict = None
+    if world == 1 and args.conv != 0 and not args.no_strict:
+        rs = pkg.Renderer(w, h, device=local, conv=0)
+        rs.upload_scene(prims)
+        rs.render_frame(uniforms(0), pkg.MODE_NONE)
+        ms, smp = 0.0, 0
+        for k in range(2):
+            rs.render_frame(uniforms(args.warmup + k), pkg.MODE_NONE)
+            ms += rs.timings().trace_ms
+            smp += rs.frame_stats().samples_traced
+        rs.close()
+        strict = {"conv": 0, "value": smp / ms / 1e3, "unit": "Msamples/s (trace kernel, device)", "trace_ms_per_step": ms / 2,
+                  "roofline_frac": fmin_per_sample * smp / (ms / 1e3) / 1e12 / NOMINAL_FP32_TFLOPS,
+                  "note": "same kernel source, one IEEE rounding per WGSL operator; bit-exact against the oracle (tests/test_gpu_parity.py)"}
+
     value = samples_total / (dev_ms / 1e3) / 1e6
     line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["label"], "samples_traced_per_step": samples_total / args.steps,
-                       "samples_nominal_per_step": w * h * wl["spp"], "conv": args.conv, "stripe_rows": args.stripe_rows,
+                       "samples_nominal_per_step": w * h * wl["spp"], "conv": args.conv,
+                       "arithmetic": {0: "strict: one IEEE rounding per WGSL operator (bit-exact vs oracle)",
+                                      1: "strict + fused vector helpers (bit-exact vs oracle conv 1)",
+                                      2: "device-native: FFMA contraction + MUFU rcp/rsqrt/sqrt/sin/cos, within north_star tolerances (tests/test_gpu_native.py)"}[args.conv],
+                       "stripe_rows": args.stripe_rows,
                        "l2": "256 MiB flush between timed steps" if small else "frame buffers (3 x %d MB) exceed the 126 MB L2" % (frame_bytes >> 20),
                        "parallelism": f"rows x{world}"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "strict": strict}
     print(json.dumps(line), flush=True)
     sr.close()
     if world > 1:
@@ -352,7 +372,9 @@ def main():
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--spp", type=int, default=0)
-    ap.add_argument("--conv", type=int, default=0, choices=[0, 1])
+    ap.add_argument("--conv", type=int, default=2, choices=[0, 1, 2],
+                    help="arithmetic convention: 2 device-native (default, the production build), 0 strict IEEE as written, 1 fused helpers")
+    ap.add_argument("--no-strict", action="store_true", help="skip the strict (conv 0) comparison leg")
     ap.add_argument("--stripe-rows", type=int, default=4)
     ap.add_argument("--count-stride", type=int, default=24, help="instrumented kernel runs on every n-th row")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

@@ -17,8 +17,8 @@ using namespace trt;
 // conv 2 lives in its own translation unit (trt_native.cu: --fmad=true -use_fast_math)
 namespace trt {
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
-                                const LightView &lv, const FrameParams &fp, int sm_count, cudaStream_t stream,
-                                uint32_t *launches);
+                                const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
+                                cudaStream_t stream, uint32_t *launches);
 }
 
 struct trt_ctx {
@@ -40,6 +40,7 @@ struct trt_ctx {
     uint32_t cap_prims = 0, cap_lights = 0, cap_runs = 0;
     SceneView sv{};
     LightView lv{};
+    SmallScene small{};                // canonical small-scene mirror for the conv 2 scan (host copy)
     bool have_scene = false;
     uint64_t scene_serial = 0;
 
@@ -215,6 +216,42 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
         if (runs.empty() || runs.back().x != (int)types[i]) runs.push_back(make_int4((int)types[i], (int)i, (int)i + 1, 0));
         else runs.back().z = (int)i + 1;
     }
+    // canonical small scene (conv 2 unrolled scan): spheres, planes, triangles in this order, few of each
+    {
+        SmallScene sm{};
+        uint32_t ns = 0, np = 0, nt = 0;
+        bool canon = true;
+        for (uint32_t i = 0; i < count && canon; i++) {
+            const uint32_t t = prims[i].primitive_type;
+            if (t == 0u) { canon = (np == 0 && nt == 0); ns++; }
+            else if (t == 1u) { canon = (nt == 0); np++; }
+            else if (t == 2u) nt++;
+            else canon = false;
+        }
+        if (canon && ns <= TRT_SMALL_S && np <= TRT_SMALL_P && nt <= TRT_SMALL_T) {
+            sm.ok = 1; sm.n_sph = (int)ns; sm.n_pl = (int)np; sm.n_tri = (int)nt;
+            for (uint32_t j = 0; j < ns; j++) {
+                const trt_primitive &p = prims[j];
+                sm.sph[j] = make_float4(p.sphere_center.x, p.sphere_center.y, p.sphere_center.z, p.sphere_radius);
+                sm.sph_r2[j] = make_float4(p.sphere_radius * p.sphere_radius, 0.0f, 0.0f, 0.0f);
+            }
+            for (uint32_t j = 0; j < np; j++) {
+                const trt_primitive &p = prims[ns + j];
+                const uint8_t ty = types[ns + j];
+                const int kind = ty >= 3 ? (ty - 3) % 3 : 3;
+                sm.pl_p[j] = make_float4(p.plane_point.x, p.plane_point.y, p.plane_point.z, 0.0f);
+                memcpy(&sm.pl_p[j].w, &kind, 4);
+                sm.pl_n[j] = make_float4(p.plane_normal.x, p.plane_normal.y, p.plane_normal.z, 0.0f);
+            }
+            for (uint32_t j = 0; j < nt; j++) {
+                const trt_primitive &p = prims[ns + np + j];
+                sm.tri_v0[j] = make_float4(p.triangle_v0.x, p.triangle_v0.y, p.triangle_v0.z, 0.0f);
+                sm.tri_e1[j] = make_float4(p.triangle_v1.x - p.triangle_v0.x, p.triangle_v1.y - p.triangle_v0.y, p.triangle_v1.z - p.triangle_v0.z, 0.0f);
+                sm.tri_e2[j] = make_float4(p.triangle_v2.x - p.triangle_v0.x, p.triangle_v2.y - p.triangle_v0.y, p.triangle_v2.z - p.triangle_v0.z, 0.0f);
+            }
+        }
+        ctx->small = sm;
+    }
     const uint32_t n_lights = (uint32_t)light_prim.size(), n_runs = (uint32_t)runs.size();
     CK(cudaStreamSynchronize(ctx->stream));
     if (count > ctx->cap_prims) {
@@ -373,7 +410,7 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
             else trace_pixel_kernel<0, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
             ctx->launches += 1;
         } else if (ctx->cfg.conv == 2u) {
-            cudaError_t e = native_trace_launch(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, fp, ctx->sm_count,
+            cudaError_t e = native_trace_launch(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, &ctx->small, fp, ctx->sm_count,
                                                 ctx->stream, &ctx->launches);
             if (e != cudaSuccess) { ctx->err = std::string("native trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
         } else {

@@ -7,6 +7,9 @@
 // compiler (naga -> driver; DESIGN.md "Arithmetic conventions").  Results track the strict build to
 // rounding noise; the tolerance tests (tests/test_gpu_native.py) state the bounds.
 #define TRT_NATIVE_TU 1
+#ifndef TRT_WV_CTAS_PER_SM
+#define TRT_WV_CTAS_PER_SM 8      // 64 registers per thread: 32 resident warps per SM (A/B: 6 -> 3083, 7 -> 3204, 8 -> 3242 Msamples/s)
+#endif
 #include "trt_kernels.cuh"
 #include "trt_persistent.cuh"
 #include "trt_wave.cuh"
@@ -14,11 +17,20 @@
 namespace trt {
 
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
-                                const LightView &lv, const FrameParams &fp, int sm_count, cudaStream_t stream,
-                                uint32_t *launches) {
-    // this translation unit has its own __constant__ mirror of the scene
+                                const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
+                                cudaStream_t stream, uint32_t *launches) {
+    // this translation unit has its own __constant__ mirrors of the scene; rebinding synchronises the device
+    static ConstOwner small_owner[64];
+    const bool rebind = device >= 0 && device < 64 && !(small_owner[device].key == ctx_key && small_owner[device].serial == serial);
     cudaError_t e = persistent_bind_scene(device, ctx_key, serial, sv, lv, stream);
     if (e != cudaSuccess) return e;
+    if (rebind) {
+        e = cudaDeviceSynchronize();
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_small, small, sizeof(SmallScene));
+        if (e != cudaSuccess) return e;
+        small_owner[device].key = ctx_key;
+        small_owner[device].serial = serial;
+    }
     e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     const uint32_t want = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;

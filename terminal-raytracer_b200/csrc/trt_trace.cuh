@@ -26,7 +26,26 @@ struct ConstScene {
 };
 static __constant__ ConstScene c_scene;      // one mirror per translation unit (strict / native builds)
 
+// Canonical small scene (conv 2 fast scan): the reference always pushes spheres, then planes, then
+// triangles (lib.rs:122-154), so a scene of at most TRT_SMALL_S/P/T of each is mirrored once more with
+// one fixed constant-bank address per primitive: the unrolled scan reads its operands straight from
+// the constant bank (no address arithmetic, no loop control, no run dispatch).  Index of sphere j is
+// j, of plane j n_sph + j, of triangle j n_sph + n_pl + j.
+#define TRT_SMALL_S 4
+#define TRT_SMALL_P 8
+#define TRT_SMALL_T 4
+struct SmallScene {
+    int ok, n_sph, n_pl, n_tri;
+    float4 sph[TRT_SMALL_S];          // (c, r)
+    float4 sph_r2[TRT_SMALL_S];       // (r*r, -, -, -)
+    float4 pl_p[TRT_SMALL_P];         // (point, kind as int bits): kind 0 / 1 / 2 = normal is +-unit x / y / z, 3 = general
+    float4 pl_n[TRT_SMALL_P];         // raw normal (general planes)
+    float4 tri_v0[TRT_SMALL_T], tri_e1[TRT_SMALL_T], tri_e2[TRT_SMALL_T];
+};
+static __constant__ SmallScene c_small;
+
 struct SrcGlobal {
+    static constexpr bool kSmall = false;
     static constexpr int kUnroll = 4;       // HBM/L2 latency: keep several primitives' loads in flight
     const SceneView &sc;
     const LightView &lv;
@@ -43,6 +62,7 @@ struct SrcGlobal {
     __device__ __forceinline__ float4 le(int k) const { return __ldg(&lv.le[k]); }
 };
 struct SrcConst {
+    static constexpr bool kSmall = true;     // the canonical small-scene mirror may be used (c_small.ok)
     static constexpr int kUnroll = 1;       // constant bank: no load latency; keep the loop body small (I-cache)
     const SceneView &sc;
     __device__ SrcConst(const SceneView &s, const LightView &) : sc(s) {}
@@ -357,6 +377,67 @@ struct Tracer {
                     if (v < 0.0f || u + v > 1.0f) continue;
                     const float t = f * V::dot(e2, q);
                     if (t > t_min && t < closest) { closest = t; best = i; }
+                }
+            }
+        }
+        return best >= 0 ? closest : -1.0f;
+    }
+
+    // conv 2, canonical small scene: the same tests in the same order, fully unrolled over fixed constant-bank
+    // slots (a slot beyond the scene's count is skipped by a warp-uniform branch)
+    __device__ __forceinline__ float scan_small_native(float3 ro, float3 rd, float t_max, int &best) {
+        const float t_min = 0.001f;
+        float closest = t_max;
+        best = -1;
+#pragma unroll
+        for (int j = 0; j < TRT_SMALL_S; j++) {
+            if (j < c_small.n_sph) {
+                uint32_t cost;
+                const float t = test_sphere(ro, rd, c_small.sph[j], c_small.sph_r2[j].x, t_min, closest, cost);
+                if (t > 0.0f) { closest = t; best = j; }
+            }
+        }
+        if (c_small.n_pl > 0) {
+            // a dead axis (|d| < 1e-4, :180) gets a NaN reciprocal: its t is NaN and fails both accept compares
+            const float nan = __int_as_float(0x7fc00000);
+            const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
+                                  fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
+#pragma unroll
+            for (int j = 0; j < TRT_SMALL_P; j++) {
+                if (j < c_small.n_pl) {
+                    const float4 p = c_small.pl_p[j];
+                    const int kind = __float_as_int(p.w);
+                    float t;
+                    if (kind == 0) t = (p.x - ro.x) * inv.x;
+                    else if (kind == 1) t = (p.y - ro.y) * inv.y;
+                    else if (kind == 2) t = (p.z - ro.z) * inv.z;
+                    else {
+                        const float3 n = xyz(c_small.pl_n[j]);
+                        const float denom = V::dot(n, rd);
+                        t = V::dot(V::sub(xyz(p), ro), n) * (fabsf(denom) >= 0.0001f ? rcp_native(denom) : nan);
+                    }
+                    if (t >= t_min && t < closest) { closest = t; best = c_small.n_sph + j; }
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < TRT_SMALL_T; j++) {
+            if (j < c_small.n_tri) {
+                const float3 e1 = xyz(c_small.tri_e1[j]), e2 = xyz(c_small.tri_e2[j]);
+                const float3 h = V::cross(rd, e2);
+                const float a = V::dot(e1, h);
+                if (!(a > -0.00001f && a < 0.00001f)) {
+                    const float f = rcp_native(a);
+                    const float3 s = V::sub(ro, xyz(c_small.tri_v0[j]));
+                    const float u = f * V::dot(s, h);
+                    if (!(u < 0.0f || u > 1.0f)) {
+                        const float3 q = V::cross(s, e1);
+                        const float v = f * V::dot(rd, q);
+                        if (!(v < 0.0f || u + v > 1.0f)) {
+                            const float t = f * V::dot(e2, q);
+                            if (t > t_min && t < closest) { closest = t; best = c_small.n_sph + c_small.n_pl + j; }
+                        }
+                    }
                 }
             }
         }

@@ -95,7 +95,13 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         // ---- the scan slot: hit_scene for this lane's ray (closest-hit or shadow alike) -------------------
         int best = -1;
         float t_hit = -1.0f;
-        if (mode != WM_DONE && fp.max_depth != 0u) t_hit = CONV == 2 ? tr.scan_native(ro, rd, t_max, best) : tr.scan_lean(ro, rd, t_max, best);
+        if (CONV == 2) {
+            // every lane scans (finished lanes keep a stale ray and ignore the result): uniform control flow
+            if (fp.max_depth != 0u)
+                t_hit = (SRC::kSmall && c_small.ok) ? tr.scan_small_native(ro, rd, t_max, best) : tr.scan_native(ro, rd, t_max, best);
+        } else if (mode != WM_DONE && fp.max_depth != 0u) {
+            t_hit = tr.scan_lean(ro, rd, t_max, best);
+        }
 
         __syncwarp();
         bool path_end = false;
@@ -165,12 +171,14 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                 const float sl = V::dot(light_normal, light_vec), ss = V::dot(hn, light_vec);
                 float cos_surface = 0.0f, cos_light = 0.0f, light_distance = 0.0f;
                 float3 light_dir = f3(0.0f, 0.0f, 0.0f);
-                if (CONV == 2) {                                  // native: one MUFU.RSQ, no branch
-                    const float inv_len = rsqrt_native(d2);
-                    light_distance = d2 * inv_len;
-                    light_dir = V::scale(light_vec, inv_len);
-                    cos_surface = fmaxf(0.0f, ss * inv_len);
-                    cos_light = fmaxf(0.0f, -(sl * inv_len));
+                if (CONV == 2) {                                  // native: the cosines' signs are those of ss and -sl
+                    if (ss > 0.0f && sl < 0.0f) {
+                        const float inv_len = rsqrt_native(d2);
+                        light_distance = d2 * inv_len;
+                        light_dir = V::scale(light_vec, inv_len);
+                        cos_surface = ss * inv_len;
+                        cos_light = -(sl * inv_len);
+                    }
                 } else if (!((sl > 0.0f && sl * sl > 1e-11f * d2) || (ss < 0.0f && ss * ss > 1e-11f * d2))) {
                     light_distance = sqrtf(d2);
                     light_dir = V::divs(light_vec, light_distance);
