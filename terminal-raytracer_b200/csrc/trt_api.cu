@@ -51,6 +51,8 @@ struct trt_ctx {
     unsigned long long *d_counters = nullptr;
     unsigned int *d_work = nullptr;
     unsigned long long *d_stats = nullptr;
+    uint32_t *d_order = nullptr;       // hand-out order of the local pixels (longest first)
+    uint32_t order_w = 0, order_h = 0; // frame size the variance buffer was last written for (0: no history)
     uint32_t *d_row_map = nullptr;     // local row -> global row
     uint64_t *d_row_src = nullptr;     // quantiser source offsets per output row
     std::vector<uint32_t> rows;        // rows owned at `rows_height`
@@ -96,7 +98,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
-                    ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map,
+                    ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
                     ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
@@ -146,6 +148,7 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         CK(cudaMalloc(&ctx->d_work, 64));
         CK(cudaMalloc(&ctx->d_stats, 64));
         CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
+        CK(cudaMalloc(&ctx->d_order, ctx->max_pixels * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_map, (size_t)cfg->max_height * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_src, (size_t)cfg->max_height * sizeof(uint64_t)));
         CK(cudaMalloc(&ctx->d_packed, ctx->max_pixels * sizeof(uint32_t)));
@@ -402,6 +405,15 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
     ctx->launches = 0;
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    // longest pixels first, predicted by the variance buffer of the previous frame of the same size
+    static const bool no_order = [] { const char *k = getenv("TRT_B200_NO_ORDER"); return k && *k == '1'; }();
+    if (!no_order && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
+        CK(cudaMemsetAsync(ctx->d_work + 4, 0, 2 * sizeof(unsigned int), ctx->stream));
+        order_pixels_kernel<<<(fp.n_local_pixels + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width,
+                                                                                     fp.n_local_pixels, ctx->d_order, ctx->d_work + 4);
+        ctx->launches += 1;
+        fp.order = ctx->d_order;
+    }
     if (fp.n_local_pixels) {
         if (ctx->cfg.count_work) {
             const uint32_t blocks = (fp.n_local_pixels + 127u) / 128u;
@@ -429,6 +441,8 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     ctx->last_u = *u;
     ctx->have_frame = true;
+    ctx->order_w = u->width;
+    ctx->order_h = u->height;
     return TRT_OK;
 }
 

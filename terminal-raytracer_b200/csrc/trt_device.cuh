@@ -37,6 +37,7 @@ struct FrameParams {
     float spp_f, base_f;
     float3 cam_pos, cam_fwd, cam_right, cam_up;
     const uint32_t *row_map;     // local row -> global row (row sharding); NULL = identity
+    const uint32_t *order;       // hand-out order of the local pixels (longest first, from the previous frame's variance); NULL = natural
     float4 *pixels, *accumulation;
     trt_variance *variance;
     unsigned long long *counters;   // trt_counters as 19 x u64 (instrumented build only)

@@ -84,6 +84,35 @@ __global__ void __launch_bounds__(128) trace_pixel_kernel(SceneView sc, LightVie
     if (COUNT) cn.flush(fp.counters);
 }
 
+// ---- hand-out order: longest pixels first ------------------------------------------------------------
+// A pixel is a serial chain (one RNG state, shader.wgsl:507-565) of base samples and, when the variance of
+// the base samples exceeds 10, up to 3x as many extra ones (:555-565): the frame's makespan is bounded by
+// the pixels started last.  The variance buffer of the previous frame (:608) predicts which pixels are
+// long; they are handed out first, the short ones fill the tail.  Scheduling only: every pixel's result is
+// independent of the order (bit-identical frames).  Two cursors fill `order` from both ends.
+static __global__ void order_pixels_kernel(const trt_variance *variance, const uint32_t *row_map, uint32_t width,
+                                           uint32_t n_local_pixels, uint32_t *order, unsigned int *cursors) {
+    const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = lp < n_local_pixels;
+    bool heavy = false;
+    if (live) {
+        const uint32_t lr = lp / width, x = lp - lr * width;
+        const uint32_t y = row_map ? row_map[lr] : lr;
+        heavy = variance[(size_t)y * width + x].variance > 10.0f;
+    }
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    const unsigned mh = __ballot_sync(0xffffffffu, live && heavy), ml = __ballot_sync(0xffffffffu, live && !heavy);
+    unsigned bh = 0, bl = 0;
+    if (lane == 0) {
+        if (mh) bh = atomicAdd(&cursors[0], __popc(mh));
+        if (ml) bl = atomicAdd(&cursors[1], __popc(ml));
+    }
+    bh = __shfl_sync(0xffffffffu, bh, 0);
+    bl = __shfl_sync(0xffffffffu, bl, 0);
+    if (live && heavy) order[bh + __popc(mh & lt)] = lp;
+    if (live && !heavy) order[n_local_pixels - 1u - (bl + __popc(ml & lt))] = lp;
+}
+
 // pack the rows this shard owns contiguously (local row order) for the NCCL gather
 static __global__ void pack_rows_kernel(const float4 *src, float4 *dst, const uint32_t *row_map, uint32_t width,
                                  uint32_t n_local_pixels) {

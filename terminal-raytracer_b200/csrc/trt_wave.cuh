@@ -65,8 +65,9 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
             if ((int)lane == leader) base = atomicAdd(fp.work_counter, __popc(need));
             base = __shfl_sync(0xffffffffu, base, leader);
             if (mode == WM_NEED_PIXEL) {
-                const uint32_t lp = base + __popc(need & lt_mask);
-                if (lp < fp.n_local_pixels) {
+                const uint32_t slot = base + __popc(need & lt_mask);
+                if (slot < fp.n_local_pixels) {
+                    const uint32_t lp = fp.order ? fp.order[slot] : slot;
                     const uint32_t lr = lp / fp.width;
                     const uint32_t x = lp - lr * fp.width;
                     const uint32_t y = fp.row_map ? fp.row_map[lr] : lr;
