@@ -13,6 +13,9 @@
 #include "trt_kernels.cuh"
 #include "trt_persistent.cuh"
 #include "trt_wave.cuh"
+#include "trt_native.cuh"
+#include <cstdlib>
+#include <cstring>
 
 namespace trt {
 
@@ -33,11 +36,29 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     }
     e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    const uint32_t want = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
-    const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
-    const uint32_t blocks = want < cap ? want : cap;
-    if (scene_fits_constant(sv)) trace_wave_kernel<2, SrcConst><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
-    else trace_wave_kernel<2, SrcGlobal><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+    // deferred-shadow kernel (trt_native.cuh) when the light count fits its queue; TRT_B200_NATIVE=wave forces the
+    // wave kernel in the same convention (A/B measurements)
+    static const bool force_wave = [] { const char *k = getenv("TRT_B200_NATIVE"); return k && !strcmp(k, "wave"); }();
+    const bool constant = scene_fits_constant(sv);
+    if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
+        static bool carveout_set = false;
+        if (!carveout_set) {
+            cudaFuncSetAttribute(trace_native_kernel<SrcConst>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            cudaFuncSetAttribute(trace_native_kernel<SrcGlobal>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            carveout_set = true;
+        }
+        const uint32_t want = (fp.n_local_pixels + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
+        const uint32_t cap = (uint32_t)sm_count * TRT_NV_CTAS_PER_SM;
+        const uint32_t blocks = want < cap ? want : cap;
+        if (constant) trace_native_kernel<SrcConst><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_native_kernel<SrcGlobal><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+    } else {
+        const uint32_t want = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
+        const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
+        const uint32_t blocks = want < cap ? want : cap;
+        if (constant) trace_wave_kernel<2, SrcConst><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_wave_kernel<2, SrcGlobal><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+    }
     *launches += 1;
     return cudaGetLastError();
 }
