@@ -310,8 +310,19 @@ def ours(args):
     trace_s = trace_sum_max / 1e3
     achieved = fmin_per_sample * samples_total / world / trace_s / 1e12 if trace_s > 0 else 0.0   # per GPU
     ffma, sms, khz = pkg.api.measure_fp32_peak(local)
-    roofline = {"bound": "fp32", "kernel": "trace_wave_kernel", "achieved": achieved, "peak": NOMINAL_FP32_TFLOPS,
-                "unit": "TFLOP/s", "frac": achieved / NOMINAL_FP32_TFLOPS, "traffic": None,
+    # DRAM bytes per launch of the trace kernel from the committed ncu --set full capture of this workload
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        ent = tj.get(f"{wl['name']}_conv{args.conv}")
+        if ent and (ent["width"], ent["height"], ent["spp"]) == (w, h, wl["spp"]) and world == 1:
+            traffic = ent["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        pass
+    roofline = {"bound": "fp32", "kernel": "trace_native_kernel" if args.conv == 2 else "trace_wave_kernel",
+                "achieved": achieved, "peak": NOMINAL_FP32_TFLOPS,
+                "unit": "TFLOP/s", "frac": achieved / NOMINAL_FP32_TFLOPS, "traffic": traffic,
+                "traffic_unit": "bytes of DRAM read + written per launch (ncu --set full, profiles/traffic.json)",
                 "peak_source": "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json holds no FP32 figure)",
                 "measured_ffma_tflops": ffma, "frac_of_measured_ffma": achieved / ffma if ffma else None,
                 "flops_min_per_sample": fmin_per_sample, "flops_written_per_sample": fwritten_per_sample,

@@ -53,6 +53,7 @@ __global__ void repack_kernel(RepackParams rp) {
         if (p.primitive_type == 0u) {
             a = f4(ld3(p.sphere_center), p.sphere_radius);
             n = make_float4(0, 0, 0, TRT_FOUR_PI_F * p.sphere_radius * p.sphere_radius);
+            c.w = fabsf(a.x) + fabsf(a.y) + fabsf(a.z) + a.w;      // magnitude scale for the reach test (trt_native.cuh)
         } else {
             float3 e1 = V::sub(ld3(p.triangle_v1), ld3(p.triangle_v0));
             float3 e2 = V::sub(ld3(p.triangle_v2), ld3(p.triangle_v0));
@@ -61,6 +62,8 @@ __global__ void repack_kernel(RepackParams rp) {
             b = f4(ld3(p.triangle_v1), 0.0f);
             c = f4(ld3(p.triangle_v2), 0.0f);
             n = f4(V::normalize(cr), 0.5f * V::length(cr));
+            b.w = V::dot(xyz(n), xyz(a));                          // plane offset of the light (reach test, trt_native.cuh)
+            c.w = fabsf(b.w);
         }
         rp.la[i] = a; rp.lb[i] = b; rp.lc[i] = c; rp.ln[i] = n;
         rp.le[i] = f4(ld3(p.emission), __int_as_float((int)p.primitive_type));

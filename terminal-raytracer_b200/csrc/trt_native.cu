@@ -36,28 +36,42 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     }
     e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    // deferred-shadow kernel (trt_native.cuh) when the light count fits its queue; TRT_B200_NATIVE=wave forces the
-    // wave kernel in the same convention (A/B measurements)
-    static const bool force_wave = [] { const char *k = getenv("TRT_B200_NATIVE"); return k && !strcmp(k, "wave"); }();
+    // deferred-NEE kernel (trt_native.cuh) when the light count fits its mask.  TRT_B200_NATIVE=wave forces the
+    // wave kernel in the same convention, =generic the unspecialised scan
+    // (A/B measurements only)
+    static const char *force = getenv("TRT_B200_NATIVE");
+    const bool force_wave = force && !strcmp(force, "wave");
+    const bool force_generic = force && !strcmp(force, "generic");
     const bool constant = scene_fits_constant(sv);
+    static bool carveout_set = false;
+    if (!carveout_set) {
+        cudaFuncSetAttribute(trace_native_kernel<SrcConst, ShapeCornell>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        carveout_set = true;
+    }
+    const uint32_t want = (fp.n_local_pixels + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
+    const uint32_t cap = (uint32_t)sm_count * TRT_NV_CTAS_PER_SM;
+    const uint32_t blocks = want < cap ? want : cap;
+    // the reference's default scene shape (3 spheres, 6 axis-aligned walls in y y x x z z order, 2 triangles)
+    // has a compile-time specialised scan; any other scene takes the same kernel with run-time counts
+    bool cornell = constant && !force_generic && small->ok && small->n_sph == ShapeCornell::NS &&
+                   small->n_pl == ShapeCornell::NP && small->n_tri == ShapeCornell::NT;
+    for (int j = 0; cornell && j < ShapeCornell::NP; j++) {
+        int kind;
+        memcpy(&kind, &small->pl_p[j].w, 4);
+        cornell = kind == ShapeCornell::kind(j);
+    }
     if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
-        static bool carveout_set = false;
-        if (!carveout_set) {
-            cudaFuncSetAttribute(trace_native_kernel<SrcConst>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            cudaFuncSetAttribute(trace_native_kernel<SrcGlobal>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-            carveout_set = true;
-        }
-        const uint32_t want = (fp.n_local_pixels + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
-        const uint32_t cap = (uint32_t)sm_count * TRT_NV_CTAS_PER_SM;
-        const uint32_t blocks = want < cap ? want : cap;
-        if (constant) trace_native_kernel<SrcConst><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
-        else trace_native_kernel<SrcGlobal><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        if (cornell) trace_native_kernel<SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else if (constant) trace_native_kernel<SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_native_kernel<SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
     } else {
-        const uint32_t want = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
-        const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
-        const uint32_t blocks = want < cap ? want : cap;
-        if (constant) trace_wave_kernel<2, SrcConst><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
-        else trace_wave_kernel<2, SrcGlobal><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        const uint32_t wwant = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
+        const uint32_t wcap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
+        const uint32_t wblocks = wwant < wcap ? wwant : wcap;
+        if (constant) trace_wave_kernel<2, SrcConst><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_wave_kernel<2, SrcGlobal><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
     }
     *launches += 1;
     return cudaGetLastError();

@@ -1,30 +1,31 @@
 // trt_native.cuh -- production trace kernel of the device-native convention (conv 2): persistent warps,
-// one path per lane, and DEFERRED shadow rays.
+// one path per lane, and DEFERRED next-event estimation.
 //
 // The wave kernel (trt_wave.cuh) gives every lane one scan slot per iteration; a lane whose bounce
 // needs a shadow ray spends its next slot on that ray and only then goes on, so that 28 % of all
 // lane-iterations of the Cornell box are shadow iterations in which the lane skips most of the shading
-// code the warp executes anyway (ncu: 20.6 of 28 live lanes in the hit / light / scatter blocks,
-// profiles/r1_native_wave_regions.txt).
+// code the warp executes anyway (profiles/r1_native_wave_regions.txt).
 //
 // Visibility only gates an addition into the sample's radiance (shader.wgsl:402-431): it influences
 // neither the random-number stream nor the path.  conv 2 is not bound to the order of floating-point
-// additions, so here a lane does NOT wait for its shadow rays:
-//   * light loop: a needed shadow ray is pushed, with its clamped contribution and its owner, onto a
-//     per-warp FIFO in shared memory; the lane goes straight on to the scatter step and traces its next
-//     closest-hit ray in the next iteration -- one full bounce per iteration for every live lane;
-//   * when 32 rays have queued up the warp spends ONE iteration on them: every lane scans one queued ray
-//     (full SIMT width) and adds the contribution of an unoccluded ray to its owner's "late" sum;
-//   * a sample is finished (shader.wgsl:548-551) only when all the shadow rays it posted are resolved;
-//     a lane whose path ends earlier waits (it is counted towards flushing the queue sooner).
-//   * triangle lights are one-sided (cos_light = max(0, dot(n_light, -dir)), :404): a shading point behind
-//     the light's plane receives nothing whatever point is sampled, so such a lane only advances its
-//     random state by the two draws; a point in front of the plane queues the WHOLE light sample (its two
-//     random numbers, the hit point and normal, colour x attenuation) and the sample point, cosines,
-//     contribution and shadow ray are computed in the queue pass at full SIMT width instead of by the few
-//     lanes of a warp that happen to see the light (Cornell box: 19 % of the hits).
+// additions, so here a lane does NOT wait for its light samples:
+//   * light loop (:342-433) in the bounce iteration: per light only the two random draws are consumed
+//     (the state moves on exactly as in the shader) and a cheap conservative test decides whether the
+//     light can reach the shading point at all -- a triangle light is one-sided (cos_light = max(0,
+//     dot(n_light, -dir)), :404), so a point behind its plane receives nothing whatever point is sampled;
+//     a sphere light entirely below the point's tangent plane likewise (cos_surface <= 0, :403);
+//   * a hit that some light may reach posts ONE entry on a per-warp FIFO in shared memory: hit point,
+//     normal, colour x attenuation, the random state before the light loop and the mask of those lights;
+//     the lane goes straight on to the scatter step -- one full bounce per iteration for every live lane;
+//   * when 32 entries have queued up the warp resolves them at full SIMT width: every lane takes one
+//     entry and, light by light (warp-uniform index: no divergence on the light type), re-derives the two
+//     draws, evaluates the light sample (:352-389), the cosines and the clamped contribution (:403-429) and
+//     scans its shadow ray (:394-400); an unoccluded contribution is added to the owner's "late" sum;
+//   * a sample is finished (:548-551) only when every entry it posted is resolved; a lane whose path ends
+//     earlier waits (waiting lanes make the queue flush sooner).
 // Per pixel the order of random draws, of samples and of bounces is the shader's; only the order in
 // which a sample's light contributions are summed differs (rounding-level, inside conv 2's tolerance).
+// There is no limit on the number of lights beyond the 16-bit mask (TRT_NV_MAX_LIGHTS).
 #pragma once
 #include "trt_kernels.cuh"
 
@@ -36,22 +37,21 @@ namespace trt {
 #ifndef TRT_NV_CTAS_PER_SM
 #define TRT_NV_CTAS_PER_SM 8
 #endif
-#define TRT_NV_RING 128          // queued shadow rays per warp (power of two)
-#define TRT_NV_MAX_LIGHTS 3      // 31 left over + 32 lanes x lights per iteration must fit the ring
+#define TRT_NV_RING 64           // queued hits per warp: at most 31 left over + 32 new ones per iteration
+#define TRT_NV_MAX_LIGHTS 16     // light mask bits in the entry's meta word
 
 enum { NM_ACTIVE = 0, NM_WAIT = 1, NM_NEED_PIXEL = 2, NM_DONE = 3 };
-// queue entry, 12 words.  kind 0 (shadow ray ready): origin, direction, t_max, contribution.
-//                         kind 1 (triangle-light sample to evaluate): hit point, normal, r1, colour x attenuation, r2.
-// meta = owner thread | light << 8 | kind << 31
-enum { RQ_W0, RQ_W1, RQ_W2, RQ_W3, RQ_W4, RQ_W5, RQ_W6, RQ_W7, RQ_W8, RQ_W9, RQ_W10, RQ_META, RQ_FIELDS };
+// queue entry, 11 words: hit point, unit normal (facing the ray), colour x attenuation, random state before
+// the light loop (advanced light by light while the entry is being resolved), meta = owner thread | mask << 8
+enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ_META, DQ_FIELDS };
 
-template <class SRC>
+template <class SRC, class SHAPE>
 __global__ void __launch_bounds__(TRT_NV_THREADS, TRT_NV_CTAS_PER_SM)
 trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
     typedef M<2> V;
     Counters<false> cn;
     Tracer<2, false, SRC> tr(sc, lv, fp, cn);
-    __shared__ float s_ring[TRT_NV_THREADS / 32][RQ_FIELDS][TRT_NV_RING];
+    __shared__ float s_ring[TRT_NV_THREADS / 32][DQ_FIELDS][TRT_NV_RING];
     __shared__ float s_late[3][TRT_NV_THREADS];
     __shared__ unsigned s_res[TRT_NV_THREADS];
     const unsigned tid = threadIdx.x, lane = tid & 31u;
@@ -63,18 +63,20 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
     __syncwarp();
 
     uint32_t head = 0, tail = 0;                 // FIFO counters, identical in every lane of the warp
-    uint32_t pend = 0;                           // shadow rays this lane has posted so far
+    int sp_k = -1;                               // >= 0: the warp is resolving the oldest entries against light sp_k
+    uint32_t pend = 0;                           // entries this lane has posted so far
     int mode = NM_NEED_PIXEL;
     uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0;
     bool extra_phase = false;
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
     float3 att = f3(1, 1, 1), acc = f3(0, 0, 0);
     float3 ro = f3(0, 0, 0), rd = f3(0, 0, 1);   // this lane's closest-hit ray
-    const bool small = SRC::kSmall && c_small.ok;
+    const bool small = SHAPE::kFixed || (SRC::kSmall && c_small.ok);
 
     for (;;) {
-        // ---- finish the sample of a lane whose path has ended and whose shadow rays are all resolved ------
+        // ---- finish the sample of a lane whose path has ended and whose queue entries are all resolved ------
         // (shader.wgsl:548-551, :555-565, :596-621)
+        bool new_ray = false;
         if (mode == NM_WAIT && *res == pend) {
             acc = V::add(acc, f3(*late_x, *late_y, *late_z));
             *late_x = 0.0f; *late_y = 0.0f; *late_z = 0.0f;
@@ -102,13 +104,8 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
                 tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value);
                 mode = NM_NEED_PIXEL;
-            } else {                                              // next sample (shader.wgsl:517 / :565)
-                rng = pcg_hash(rng + si * 5096u);
-                tr.camera_ray(rng, xy & 0xffffu, xy >> 16, ro, rd);
-                att = f3(1.0f, 1.0f, 1.0f);
-                acc = f3(0.0f, 0.0f, 0.0f);
-                depth = 0;
-                mode = NM_ACTIVE;
+            } else {
+                new_ray = true;
             }
         }
 
@@ -133,81 +130,120 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     si = 0;
                     target = fp.base_samples;
                     extra_phase = false;
-                    rng = pcg_hash(rng);                         // first sample of the pixel (shader.wgsl:517-546)
-                    tr.camera_ray(rng, x, y, ro, rd);
-                    att = f3(1.0f, 1.0f, 1.0f);
-                    acc = f3(0.0f, 0.0f, 0.0f);
-                    depth = 0;
-                    mode = NM_ACTIVE;
+                    new_ray = true;
                 } else {
                     mode = NM_DONE;
                 }
             }
         }
+        // ---- next sample of the pixel: reseed (shader.wgsl:517 / :565; si = 0 for a new pixel), camera ray ----
+        if (new_ray) {
+            rng = pcg_hash(rng + si * 5096u);
+            tr.camera_ray(rng, xy & 0xffffu, xy >> 16, ro, rd);
+            att = f3(1.0f, 1.0f, 1.0f);
+            acc = f3(0.0f, 0.0f, 0.0f);
+            depth = 0;
+            mode = NM_ACTIVE;
+        }
         if (__all_sync(0xffffffffu, mode == NM_DONE)) break;
 
-        // ---- this iteration's scan: the queued shadow rays (when enough have queued up, or lanes are waiting
-        // for them) or every lane's own closest-hit ray ------------------------------------------------------------
-        const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
-        const unsigned m_wait = __ballot_sync(0xffffffffu, mode == NM_WAIT);
+        // ---- this iteration's scan: one light of the queued hits (when enough have queued up, or lanes are
+        // waiting for them) or every lane's own closest-hit ray ------------------------------------------------------
         const uint32_t cnt = tail - head;
-        const bool spass = cnt >= 32u || (cnt > 0u && (cnt + 2u * __popc(m_wait) >= 32u || !m_active));
+        if (sp_k < 0 && cnt > 0u) {
+            const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
+            const unsigned m_wait = __ballot_sync(0xffffffffu, mode == NM_WAIT);
+            if (cnt >= 32u || cnt + 2u * __popc(m_wait) >= 32u || !m_active) sp_k = 0;
+        }
+        const bool spass = sp_k >= 0;
         float3 qo = ro, qd = rd, qc = f3(0, 0, 0);
         float qt = 1e10f;
-        unsigned qowner = 0;
+        unsigned qowner = 0, qrest = 0;
+        uint32_t qrng = 0;
         bool qneed = false;
         const uint32_t qn = cnt < 32u ? cnt : 32u;
         const uint32_t qe = (head + lane) & (TRT_NV_RING - 1u);
         const bool qvalid = spass && lane < qn;
-        if (qvalid) {
-            const unsigned meta = __float_as_uint(ring[RQ_META][qe]);
-            qowner = meta & 0xffu;
-            const float3 w0 = f3(ring[RQ_W0][qe], ring[RQ_W1][qe], ring[RQ_W2][qe]);
-            const float3 w3 = f3(ring[RQ_W3][qe], ring[RQ_W4][qe], ring[RQ_W5][qe]);
-            const float w6 = ring[RQ_W6][qe];
-            const float3 w7 = f3(ring[RQ_W7][qe], ring[RQ_W8][qe], ring[RQ_W9][qe]);
-            if (meta >> 31) {                                     // triangle-light sample :370-431, evaluated here
-                const int k = (int)((meta >> 8) & 0xffu);
-                const float r2 = ring[RQ_W10][qe];
+        if (spass) {
+            unsigned lmask = 0;
+            if (qvalid) {
+                const unsigned meta = __float_as_uint(ring[DQ_META][qe]);
+                qowner = meta & 0xffu;
+                lmask = meta >> 8;
+                qrng = __float_as_uint(ring[DQ_RNG][qe]);
+            }
+            const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
+            int k = sp_k;
+            while (!((uni >> k) & 1u)) {                          // lights no queued hit can see: only their draws
+                qrng = pcg_hash(pcg_hash(qrng));
+                k++;
+            }
+            sp_k = k;
+            qrest = uni >> (k + 1);
+            const uint32_t s1 = pcg_hash(qrng);                   // the two draws of :350-351 / :371-372, in order
+            qrng = pcg_hash(s1);
+            qt = -1.0f;                                           // nothing to find unless the sample is needed
+            if ((lmask >> k) & 1u) {
+                const float r1 = __uint2float_rn(s1) * 2.3283064365386963e-10f;
+                const float r2 = __uint2float_rn(qrng) * 2.3283064365386963e-10f;
+                const float3 P = f3(ring[DQ_PX][qe], ring[DQ_PY][qe], ring[DQ_PZ][qe]);
+                const float3 N = f3(ring[DQ_NX][qe], ring[DQ_NY][qe], ring[DQ_NZ][qe]);
+                const float4 a = tr.src.la(k);
                 const float4 nl = tr.src.ln(k);
                 const float4 em = tr.src.le(k);
-                const float sqrt_r1 = sqrt_native(w6);
-                const float u = 1.0f - sqrt_r1;
-                const float v = r2 * sqrt_r1;
-                const float3 light_point = V::lin3(xyz(tr.src.la(k)), 1.0f - u - v, xyz(tr.src.lb(k)), u, xyz(tr.src.lc(k)), v);
-                const float3 light_vec = V::sub(light_point, w0);
-                const float sl = V::dot(xyz(nl), light_vec), ss = V::dot(w3, light_vec);
-                qo = V::axpy(w0, w3, 0.001f);                     // :394-399
-                qt = -1.0f;                                       // nothing to find unless the sample is needed
+                float3 light_vec;
+                float sl;
+                if (__float_as_int(em.w) == 0) {                  // uniform sphere sampling :352-369
+                    const float cos_theta = 1.0f - 2.0f * r1;
+                    const float sin_theta = sqrt_native(1.0f - cos_theta * cos_theta);
+                    float sp, cp;
+                    sincos_turn<2>(r2, sp, cp);
+                    const float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
+                    light_vec = V::sub(V::axpy(xyz(a), local, a.w), P);
+                    sl = V::dot(local, light_vec);
+                } else {                                          // uniform triangle sampling :370-389
+                    const float sqrt_r1 = sqrt_native(r1);
+                    const float u = 1.0f - sqrt_r1;
+                    const float v = r2 * sqrt_r1;
+                    const float3 light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(tr.src.lb(k)), u, xyz(tr.src.lc(k)), v);
+                    light_vec = V::sub(light_point, P);
+                    sl = V::dot(xyz(nl), light_vec);
+                }
+                const float ss = V::dot(N, light_vec);
                 if (ss > 0.0f && sl < 0.0f) {                     // both cosines positive (:403-404)
                     qneed = true;
                     const float d2 = V::dot(light_vec, light_vec);
                     const float inv_len = rsqrt_native(d2);
+                    qo = V::axpy(P, N, 0.001f);                   // :394-399
                     qd = V::scale(light_vec, inv_len);
                     qt = d2 * inv_len - 0.001f;
                     const float geometric = ((ss * inv_len) * -(sl * inv_len)) * rcp_native(d2);
-                    const float3 cc = V::mulv(V::scale(w7, 0.31830988618f), V::scale(xyz(em), geometric * nl.w));
+                    const float3 C = f3(ring[DQ_CX][qe], ring[DQ_CY][qe], ring[DQ_CZ][qe]);
+                    const float3 cc = V::mulv(V::scale(C, 0.31830988618f), V::scale(xyz(em), geometric * nl.w));
                     qc = f3(fminf(cc.x, 10.0f), fminf(cc.y, 10.0f), fminf(cc.z, 10.0f));
                 }
-            } else {
-                qo = w0; qd = w3; qt = w6; qc = w7;
-                qneed = true;
             }
         }
         int best = -1;
         float t_hit = -1.0f;
-        if (fp.max_depth != 0u) t_hit = small ? tr.scan_small_native(qo, qd, qt, best) : tr.scan_native(qo, qd, qt, best);
+        if (fp.max_depth != 0u) t_hit = small ? tr.template scan_small_native<SHAPE>(qo, qd, qt, best) : tr.scan_native(qo, qd, qt, best);
 
-        if (spass) {                                              // shader.wgsl:402-431 for the queued rays
+        if (spass) {                                              // shader.wgsl:402-431 for the queued hits
             if (qvalid) {
                 if (t_hit < 0.0f && qneed) {
                     atomicAdd(&s_late[0][qowner], qc.x);
                     atomicAdd(&s_late[1][qowner], qc.y);
                     atomicAdd(&s_late[2][qowner], qc.z);
                 }
-                atomicAdd(&s_res[qowner], 1u);
+                if (qrest) ring[DQ_RNG][qe] = __uint_as_float(qrng);
+                else atomicAdd(&s_res[qowner], 1u);
             }
-            head += qn;
+            if (qrest) {
+                sp_k++;
+            } else {
+                sp_k = -1;
+                head += qn;
+            }
             __syncwarp();
             continue;
         }
@@ -236,72 +272,39 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
             }
         }
 
-        // ---- next-event estimation (shader.wgsl:342-433): every light in order, two draws each; a needed
-        // shadow ray goes to the queue with its clamped contribution ----------------------------------------------
+        // ---- next-event estimation, bounce side (shader.wgsl:342-433): every light in order consumes its two
+        // draws; the samples themselves are evaluated when the queue is resolved ------------------------------------
+        const uint32_t rng0 = rng;
+        unsigned lmask = 0;
+        const float hp_mag = 1.0f + fabsf(hp.x) + fabsf(hp.y) + fabsf(hp.z);
         for (int k = 0; k < sc.n_lights; k++) {
-            const float4 a = tr.src.la(k);
-            const float4 nl = tr.src.ln(k);
-            const float4 em = tr.src.le(k);
-            bool post = false;
-            float3 w0 = f3(0, 0, 0), w3 = f3(0, 0, 1), w7 = f3(0, 0, 0);
-            float w6 = 0.0f, w10 = 0.0f;
-            unsigned kind = 0;
-            if (__float_as_int(em.w) == 0) {                      // sphere light :352-369 -> a ready shadow ray
-                if (hit) {
-                    const float r1 = rnd(rng), r2 = rnd(rng);
-                    const float cos_theta = 1.0f - 2.0f * r1;
-                    const float sin_theta = sqrt_native(1.0f - cos_theta * cos_theta);
-                    float sp, cp;
-                    sincos_turn<2>(r2, sp, cp);
-                    const float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
-                    const float3 light_vec = V::sub(V::axpy(xyz(a), local, a.w), hp);
-                    const float sl = V::dot(local, light_vec), ss = V::dot(hn, light_vec);
-                    if (ss > 0.0f && sl < 0.0f) {                 // both cosines positive (:403-404)
-                        const float d2 = V::dot(light_vec, light_vec);
-                        const float inv_len = rsqrt_native(d2);
-                        w0 = V::axpy(hp, hn, 0.001f);             // :394-399
-                        w3 = V::scale(light_vec, inv_len);
-                        w6 = d2 * inv_len - 0.001f;
-                        const float geometric = ((ss * inv_len) * -(sl * inv_len)) * rcp_native(d2);
-                        const float3 brdf = V::scale(xyz(mc), 0.31830988618f);
-                        const float3 cc = V::mulv(V::mulv(brdf, xyz(em)), V::scale(att, geometric * nl.w));
-                        w7 = f3(fminf(cc.x, 10.0f), fminf(cc.y, 10.0f), fminf(cc.z, 10.0f));
-                        post = true;
-                    }
-                }
-            } else {                                              // triangle light :370-389 -> queue the sample
-                // plane offset of the light and a margin for the roundings of the sample point (a convex
-                // combination of the vertices) and of the two dot products
-                const float c_l = V::dot(xyz(nl), xyz(a));
-                if (hit) {
-                    const uint32_t s1 = pcg_hash(rng);
-                    rng = pcg_hash(s1);                           // the two draws of :371-372, in order
-                    const float side = V::dot(xyz(nl), hp) - c_l;
-                    const float eps = 1e-5f * (1.0f + fabsf(c_l) + fabsf(hp.x) + fabsf(hp.y) + fabsf(hp.z));
-                    if (side > -eps) {                            // in front of the light's plane: it may shine here
-                        w0 = hp; w3 = hn;
-                        w6 = __uint2float_rn(s1) * 2.3283064365386963e-10f;
-                        w10 = __uint2float_rn(rng) * 2.3283064365386963e-10f;
-                        w7 = V::mulv(xyz(mc), att);
-                        kind = 1u;
-                        post = true;
-                    }
-                }
+            const uint32_t adv = pcg_hash(pcg_hash(rng));
+            // a quantity that must be positive for the light to contribute, with a margin for the roundings of
+            // the sample point and of the dot products (lb.w, lc.w: repack_kernel)
+            float side;
+            if (__float_as_int(tr.src.le(k).w) == 0) {            // sphere: some of it above the tangent plane
+                const float4 a = tr.src.la(k);
+                side = V::dot(hn, V::sub(xyz(a), hp)) + a.w;
+            } else {                                              // triangle: the point in front of its plane
+                side = V::dot(xyz(tr.src.ln(k)), hp) - tr.src.lb(k).w;
             }
-            const unsigned mp = __ballot_sync(0xffffffffu, post);
-            if (mp) {
-                if (post) {
-                    const uint32_t e = (tail + __popc(mp & lt_mask)) & (TRT_NV_RING - 1u);
-                    ring[RQ_W0][e] = w0.x; ring[RQ_W1][e] = w0.y; ring[RQ_W2][e] = w0.z;
-                    ring[RQ_W3][e] = w3.x; ring[RQ_W4][e] = w3.y; ring[RQ_W5][e] = w3.z;
-                    ring[RQ_W6][e] = w6;
-                    ring[RQ_W7][e] = w7.x; ring[RQ_W8][e] = w7.y; ring[RQ_W9][e] = w7.z;
-                    ring[RQ_W10][e] = w10;
-                    ring[RQ_META][e] = __uint_as_float(tid | ((unsigned)k << 8) | (kind << 31));
-                    pend++;
-                }
-                tail += __popc(mp);
+            if (hit) {
+                rng = adv;
+                if (side > -1e-5f * (hp_mag + tr.src.lc(k).w)) lmask |= 1u << k;
             }
+        }
+        const unsigned mp = __ballot_sync(0xffffffffu, lmask != 0u);
+        if (mp) {
+            if (lmask) {
+                const uint32_t e = (tail + __popc(mp & lt_mask)) & (TRT_NV_RING - 1u);
+                ring[DQ_PX][e] = hp.x; ring[DQ_PY][e] = hp.y; ring[DQ_PZ][e] = hp.z;
+                ring[DQ_NX][e] = hn.x; ring[DQ_NY][e] = hn.y; ring[DQ_NZ][e] = hn.z;
+                ring[DQ_CX][e] = mc.x * att.x; ring[DQ_CY][e] = mc.y * att.y; ring[DQ_CZ][e] = mc.z * att.z;
+                ring[DQ_RNG][e] = __uint_as_float(rng0);
+                ring[DQ_META][e] = __uint_as_float(tid | (lmask << 8));
+                pend++;
+            }
+            tail += __popc(mp);
         }
         __syncwarp();
 

@@ -6,7 +6,7 @@
 namespace trt {
 
 struct LightView {               // emissive spheres / triangles in scan order (shader.wgsl:342-392)
-    const float4 *la, *lb, *lc;  // sphere: la = (c, r); triangle: la = v0, lb = v1, lc = v2
+    const float4 *la, *lb, *lc;  // sphere: la = (c, r); triangle: la = v0, lb = v1, lc = v2; lb.w = dot(n, v0), lc.w = magnitude scale
     const float4 *ln;            // (light normal xyz [triangle], area)
     const float4 *le;            // (emission rgb, type as float bits)
 };
@@ -77,6 +77,20 @@ struct SrcConst {
     __device__ __forceinline__ float4 ln(int k) const { return c_scene.ln[k]; }
     __device__ __forceinline__ float4 le(int k) const { return c_scene.le[k]; }
 };
+
+// Compile-time description of a canonical small scene for scan_small_native: primitive counts and the
+// kind of every plane (2 bits each, first plane in the low bits; kinds as in SmallScene::pl_p.w).
+struct ShapeAny { static constexpr bool kFixed = false; static constexpr int NS = 0, NP = 0, NT = 0;
+                  static __device__ __forceinline__ constexpr int kind(int) { return 3; } };
+template <int NS_, int NP_, int NT_, unsigned KINDS_> struct ShapeFixed {
+    static constexpr bool kFixed = true;
+    static constexpr int NS = NS_, NP = NP_, NT = NT_;
+    static constexpr unsigned KINDS = KINDS_;
+    static __host__ __device__ __forceinline__ constexpr int kind(int j) { return (int)((KINDS_ >> (2 * j)) & 3u); }
+};
+// the reference's embedded default scene (lib.rs:107, src/scenes/Cornell_Box.json): 3 spheres, floor / ceiling
+// (y), right / left (x), front / back (z) walls, 2 triangles
+typedef ShapeFixed<3, 6, 2, 0xA05u> ShapeCornell;
 
 template <int CONV, bool COUNT, class SRC>
 struct Tracer {
@@ -384,29 +398,35 @@ struct Tracer {
     }
 
     // conv 2, canonical small scene: the same tests in the same order, fully unrolled over fixed constant-bank
-    // slots (a slot beyond the scene's count is skipped by a warp-uniform branch)
+    // slots (a slot beyond the scene's count is skipped by a warp-uniform branch).  With a compile-time SHAPE
+    // (ShapeFixed: primitive counts and plane kinds known to the compiler) the slot checks and the per-plane
+    // kind dispatch vanish: a plane test is one subtract, one multiply and the accept.
+    template <class SHAPE>
     __device__ __forceinline__ float scan_small_native(float3 ro, float3 rd, float t_max, int &best) {
         const float t_min = 0.001f;
         float closest = t_max;
         best = -1;
+        const int n_sph = SHAPE::kFixed ? SHAPE::NS : c_small.n_sph;
+        const int n_pl = SHAPE::kFixed ? SHAPE::NP : c_small.n_pl;
+        const int n_tri = SHAPE::kFixed ? SHAPE::NT : c_small.n_tri;
 #pragma unroll
         for (int j = 0; j < TRT_SMALL_S; j++) {
-            if (j < c_small.n_sph) {
+            if (j < n_sph) {
                 uint32_t cost;
                 const float t = test_sphere(ro, rd, c_small.sph[j], c_small.sph_r2[j].x, t_min, closest, cost);
                 if (t > 0.0f) { closest = t; best = j; }
             }
         }
-        if (c_small.n_pl > 0) {
+        if (n_pl > 0) {
             // a dead axis (|d| < 1e-4, :180) gets a NaN reciprocal: its t is NaN and fails both accept compares
             const float nan = __int_as_float(0x7fc00000);
             const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
                                   fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
 #pragma unroll
             for (int j = 0; j < TRT_SMALL_P; j++) {
-                if (j < c_small.n_pl) {
+                if (j < n_pl) {
                     const float4 p = c_small.pl_p[j];
-                    const int kind = __float_as_int(p.w);
+                    const int kind = SHAPE::kFixed ? SHAPE::kind(j) : __float_as_int(p.w);
                     float t;
                     if (kind == 0) t = (p.x - ro.x) * inv.x;
                     else if (kind == 1) t = (p.y - ro.y) * inv.y;
@@ -416,13 +436,13 @@ struct Tracer {
                         const float denom = V::dot(n, rd);
                         t = V::dot(V::sub(xyz(p), ro), n) * (fabsf(denom) >= 0.0001f ? rcp_native(denom) : nan);
                     }
-                    if (t >= t_min && t < closest) { closest = t; best = c_small.n_sph + j; }
+                    if (t >= t_min && t < closest) { closest = t; best = n_sph + j; }
                 }
             }
         }
 #pragma unroll
         for (int j = 0; j < TRT_SMALL_T; j++) {
-            if (j < c_small.n_tri) {
+            if (j < n_tri) {
                 const float3 e1 = xyz(c_small.tri_e1[j]), e2 = xyz(c_small.tri_e2[j]);
                 const float3 h = V::cross(rd, e2);
                 const float a = V::dot(e1, h);
@@ -435,7 +455,7 @@ struct Tracer {
                         const float v = f * V::dot(rd, q);
                         if (!(v < 0.0f || u + v > 1.0f)) {
                             const float t = f * V::dot(e2, q);
-                            if (t > t_min && t < closest) { closest = t; best = c_small.n_sph + c_small.n_pl + j; }
+                            if (t > t_min && t < closest) { closest = t; best = n_sph + n_pl + j; }
                         }
                     }
                 }

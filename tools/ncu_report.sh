@@ -1,7 +1,7 @@
 #!/bin/bash
 # usage (here, no GPU): tools/ncu_report.sh <tag> <kernel-substring> [top_n]  -> per-line table + key raw metrics
 tag=$1; k=$2; top=${3:-40}
-d=$(mktemp -d); ( cd $d && cuobjdump -xelf all /root/repo/terminal-raytracer_b200/libtrt_b200.so >/dev/null && nvdisasm -g -c trt_api.sm_100a.cubin > all.dis 2>&1 )
+d=$(mktemp -d); ( cd $d && cuobjdump -xelf all /root/repo/terminal-raytracer_b200/libtrt_b200.so >/dev/null && for c in trt_api trt_native; do nvdisasm -g -c $c.sm_100a.cubin; done > all.dis 2>&1 )
 ncu -i gpurun_out/prof_$tag.ncu-rep --page source --csv 2>/dev/null > $d/src.csv
 ncu -i gpurun_out/prof_$tag.ncu-rep --page raw --csv 2>/dev/null > $d/raw.csv
 python - $d/raw.csv <<'PY'
