@@ -145,7 +145,7 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         CK(cudaMemsetAsync(ctx->d_variance, 0, ctx->max_pixels * sizeof(trt_variance), ctx->stream));
         CK(cudaMalloc(&ctx->d_counters, K_COUNT * sizeof(unsigned long long)));
         CK(cudaMemsetAsync(ctx->d_counters, 0, K_COUNT * sizeof(unsigned long long), ctx->stream));
-        CK(cudaMalloc(&ctx->d_work, 64));
+        CK(cudaMalloc(&ctx->d_work, 64 + 2 * TRT_ORDER_BUCKETS * sizeof(unsigned int)));
         CK(cudaMalloc(&ctx->d_stats, 64));
         CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
         CK(cudaMalloc(&ctx->d_order, ctx->max_pixels * sizeof(uint32_t)));
@@ -408,9 +408,13 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     // longest pixels first, predicted by the variance buffer of the previous frame of the same size
     static const bool no_order = [] { const char *k = getenv("TRT_B200_NO_ORDER"); return k && *k == '1'; }();
     if (!no_order && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
-        CK(cudaMemsetAsync(ctx->d_work + 4, 0, 2 * sizeof(unsigned int), ctx->stream));
-        order_pixels_kernel<<<(fp.n_local_pixels + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width,
-                                                                                     fp.n_local_pixels, ctx->d_order, ctx->d_work + 4);
+        CK(cudaMemsetAsync(ctx->d_work + 16, 0, 2 * TRT_ORDER_BUCKETS * sizeof(unsigned int), ctx->stream));
+        const uint32_t ob = (fp.n_local_pixels + 255u) / 256u;
+        order_count_kernel<<<ob, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width, fp.n_local_pixels, fp.base_samples,
+                                                       fp.spp, ctx->d_work + 16);
+        order_scatter_kernel<<<ob, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width, fp.n_local_pixels, fp.base_samples,
+                                                         fp.spp, ctx->d_work + 16, ctx->d_order);
+        ctx->launches += 1;
         ctx->launches += 1;
         fp.order = ctx->d_order;
     }

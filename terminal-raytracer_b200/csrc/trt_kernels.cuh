@@ -89,31 +89,57 @@ __global__ void __launch_bounds__(128) trace_pixel_kernel(SceneView sc, LightVie
 
 // ---- hand-out order: longest pixels first ------------------------------------------------------------
 // A pixel is a serial chain (one RNG state, shader.wgsl:507-565) of base samples and, when the variance of
-// the base samples exceeds 10, up to 3x as many extra ones (:555-565): the frame's makespan is bounded by
-// the pixels started last.  The variance buffer of the previous frame (:608) predicts which pixels are
-// long; they are handed out first, the short ones fill the tail.  Scheduling only: every pixel's result is
-// independent of the order (bit-identical frames).  Two cursors fill `order` from both ends.
-static __global__ void order_pixels_kernel(const trt_variance *variance, const uint32_t *row_map, uint32_t width,
-                                           uint32_t n_local_pixels, uint32_t *order, unsigned int *cursors) {
+// the base samples exceeds 10, up to 3x as many extra ones (:555-565): at 1024 spp the longest chain runs
+// for tens of milliseconds, and the frame's makespan is bounded by the pixels started last.  The variance
+// buffer of the previous frame (:608) predicts every pixel's sample count by the shader's own rule (:559-562);
+// a counting sort over TRT_ORDER_BUCKETS classes of predicted length hands the longest pixels out first and
+// lets the shortest fill the tail.  Scheduling only: a pixel's result is independent of the order
+// (bit-identical frames).  order_count_kernel builds the histogram, order_scatter_kernel places the pixels
+// (order inside a class is arbitrary).
+#define TRT_ORDER_BUCKETS 32
+__device__ __forceinline__ uint32_t order_bucket(const trt_variance *variance, const uint32_t *row_map, uint32_t width, uint32_t lp,
+                                                 uint32_t base_samples, uint32_t spp) {
+    const uint32_t lr = lp / width, x = lp - lr * width;
+    const uint32_t y = row_map ? row_map[lr] : lr;
+    const float v = variance[(size_t)y * width + x].variance;
+    uint32_t predicted = base_samples;
+    if (v > 10.0f && base_samples < spp) predicted += min(spp - base_samples, __float2uint_rz(v * 50.0f));
+    const uint32_t cls = (uint32_t)(((uint64_t)predicted * (TRT_ORDER_BUCKETS - 1)) / (spp ? spp : 1u));
+    return (TRT_ORDER_BUCKETS - 1u) - min(cls, (uint32_t)TRT_ORDER_BUCKETS - 1u);        // bucket 0 = longest
+}
+static __global__ void order_count_kernel(const trt_variance *variance, const uint32_t *row_map, uint32_t width,
+                                          uint32_t n_local_pixels, uint32_t base_samples, uint32_t spp, unsigned int *hist) {
+    __shared__ unsigned int sh[TRT_ORDER_BUCKETS];
+    if (threadIdx.x < TRT_ORDER_BUCKETS) sh[threadIdx.x] = 0u;
+    __syncthreads();
     const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp < n_local_pixels) atomicAdd(&sh[order_bucket(variance, row_map, width, lp, base_samples, spp)], 1u);
+    __syncthreads();
+    if (threadIdx.x < TRT_ORDER_BUCKETS && sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], sh[threadIdx.x]);
+}
+// hist[0..B) = class sizes, hist[B..2B) = cursors (zeroed by the host)
+static __global__ void order_scatter_kernel(const trt_variance *variance, const uint32_t *row_map, uint32_t width,
+                                            uint32_t n_local_pixels, uint32_t base_samples, uint32_t spp, unsigned int *hist,
+                                            uint32_t *order) {
+    __shared__ unsigned int cnt[TRT_ORDER_BUCKETS], start[TRT_ORDER_BUCKETS], base[TRT_ORDER_BUCKETS];
+    if (threadIdx.x < TRT_ORDER_BUCKETS) cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t b = 0, rank = 0;
     const bool live = lp < n_local_pixels;
-    bool heavy = false;
     if (live) {
-        const uint32_t lr = lp / width, x = lp - lr * width;
-        const uint32_t y = row_map ? row_map[lr] : lr;
-        heavy = variance[(size_t)y * width + x].variance > 10.0f;
+        b = order_bucket(variance, row_map, width, lp, base_samples, spp);
+        rank = atomicAdd(&cnt[b], 1u);
     }
-    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    const unsigned mh = __ballot_sync(0xffffffffu, live && heavy), ml = __ballot_sync(0xffffffffu, live && !heavy);
-    unsigned bh = 0, bl = 0;
-    if (lane == 0) {
-        if (mh) bh = atomicAdd(&cursors[0], __popc(mh));
-        if (ml) bl = atomicAdd(&cursors[1], __popc(ml));
+    __syncthreads();
+    if (threadIdx.x < TRT_ORDER_BUCKETS) {
+        unsigned int off = 0;
+        for (uint32_t i = 0; i < threadIdx.x; i++) off += hist[i];
+        start[threadIdx.x] = off;
+        base[threadIdx.x] = cnt[threadIdx.x] ? atomicAdd(&hist[TRT_ORDER_BUCKETS + threadIdx.x], cnt[threadIdx.x]) : 0u;
     }
-    bh = __shfl_sync(0xffffffffu, bh, 0);
-    bl = __shfl_sync(0xffffffffu, bl, 0);
-    if (live && heavy) order[bh + __popc(mh & lt)] = lp;
-    if (live && !heavy) order[n_local_pixels - 1u - (bl + __popc(ml & lt))] = lp;
+    __syncthreads();
+    if (live) order[start[b] + base[b] + rank] = lp;
 }
 
 // pack the rows this shard owns contiguously (local row order) for the NCCL gather
