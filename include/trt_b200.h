@@ -144,6 +144,17 @@ int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32_t count);
  * mode TRT_MODE_NONE skips quantise and copy (out may be NULL).  *len = bytes written (or needed). */
 int trt_render_frame(trt_ctx *ctx, const trt_uniforms *u, int mode, uint8_t *out, size_t cap, size_t *len);
 
+/* n iterations of the reference's frame loop (lib.rs:414-560) in one call: the frames of a still camera --
+ * u[0..n) equal in everything but seed and frame_number -- are traced by ONE launch over n x pixels work items
+ * and blended in frame order (shader.wgsl:610-619), so accumulation / pixels / variance end up bit-identical to
+ * n trt_render_frame calls.  emit_all != 0: the byte streams of all n frames, back to back, go to `out`
+ * (frame_len[i] = bytes of frame i, may be NULL); emit_all == 0: only the last frame's stream (what a
+ * terminal would still be showing).  mode TRT_MODE_NONE: no stream.  Frames are processed in chunks that
+ * keep the staging buffers (16 B per pixel and frame, plus the streams) within 6 GB.  A sharded context
+ * accepts TRT_MODE_NONE only. */
+int trt_render_frames(trt_ctx *ctx, const trt_uniforms *u, uint32_t n, int mode, int emit_all, uint8_t *out, size_t cap,
+                      size_t *len, size_t *frame_len_or_null);
+
 /* the two halves of trt_render_frame, asynchronous on the context's stream (device-resident use:
  * benchmarks, multi-GPU drivers).  trt_sync waits for the stream. */
 int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u);

@@ -104,6 +104,8 @@ SYMBOLS = {
     "trt_last_error": (C.c_char_p, [_P]),
     "trt_upload_scene": (C.c_int, [_P, _P, C.c_uint32]),
     "trt_render_frame": (C.c_int, [_P, C.POINTER(Uniforms), C.c_int, _P, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "trt_render_frames": (C.c_int, [_P, C.POINTER(Uniforms), C.c_uint32, C.c_int, C.c_int, _P, C.c_size_t, C.POINTER(C.c_size_t),
+                                    C.POINTER(C.c_size_t)]),
     "trt_trace_async": (C.c_int, [_P, C.POINTER(Uniforms)]),
     "trt_quantise_async": (C.c_int, [_P, C.c_int, C.POINTER(C.c_size_t)]),
     "trt_sync": (C.c_int, [_P]),
@@ -304,6 +306,30 @@ class Renderer:
         n = C.c_size_t()
         self._ck(lib().trt_render_frame(self.h, C.byref(u), mode, p, cap, C.byref(n)))
         return C.string_at(p, n.value)
+
+    def render_frames(self, us, mode=MODE_ASCII, emit_all=False):
+        """Frame batch (trt_render_frames): `us` = uniforms of the frames of a still camera.  Returns the list of
+        byte streams of all frames (emit_all) or [last frame's stream]; [] for MODE_NONE."""
+        n = len(us)
+        arr = (Uniforms * n)(*us)
+        self.size = (us[0].width, us[0].height)
+        if mode == MODE_NONE:
+            self._ck(lib().trt_render_frames(self.h, arr, n, mode, 0, None, 0, None, None))
+            return []
+        per = us[0].width * us[0].height * 26 + 2 * us[0].height + 64
+        cap = per * (n if emit_all else 1)
+        p, _ = self._host_out(cap)
+        total = C.c_size_t()
+        lens = (C.c_size_t * n)()
+        self._ck(lib().trt_render_frames(self.h, arr, n, mode, 1 if emit_all else 0, p, cap, C.byref(total), lens))
+        if not emit_all:
+            return [C.string_at(p, total.value)]
+        out, off = [], 0
+        for i in range(n):
+            out.append(C.string_at(p.value + off, lens[i]))
+            off += lens[i]
+        assert off == total.value
+        return out
 
     def render_frame_into(self, u: Uniforms, mode, host_ptr, cap) -> int:
         """Zero-copy variant for the benchmark: bytes land in the caller's (pinned) buffer."""

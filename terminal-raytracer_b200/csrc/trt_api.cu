@@ -16,6 +16,8 @@ using namespace trt;
 
 // conv 2 lives in its own translation unit (trt_native.cu: --fmad=true -use_fast_math)
 namespace trt {
+cudaError_t native_blend_launch(float4 *cur, const uint2 *batch, uint32_t n_batch, uint32_t n_local_pixels, const uint32_t *row_map,
+                                uint32_t width, float4 *accumulation, float4 *pixels, cudaStream_t stream);
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
                                 cudaStream_t stream, uint32_t *launches);
@@ -67,6 +69,16 @@ struct trt_ctx {
     uint32_t last_q_blocks = 0;
     bool have_stream = false;
 
+    // frame batch (trt_render_frames)
+    float4 *d_batch_cur = nullptr;     // [frames of one chunk][local pixels]
+    uint2 *d_batch = nullptr;          // (seed, frame_number) per frame of the chunk
+    size_t batch_cur_cap = 0;          // in float4
+    uint32_t batch_cap = 0;
+    uint8_t *d_batch_stream = nullptr; // [frames of one chunk][stride] byte streams when every frame is emitted
+    size_t batch_stream_cap = 0;
+    uint64_t *h_batch_len = nullptr;   // pinned, one length per frame of the chunk
+    size_t batch_len_cap = 0;
+
     trt_uniforms last_u{};
     bool have_frame = false;
     trt_timings tm{};
@@ -99,9 +111,10 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
                     ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
-                    ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream};
+                    ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
+    if (ctx->h_batch_len) cudaFreeHost(ctx->h_batch_len);
     for (auto &e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -374,8 +387,9 @@ static int check_uniforms(trt_ctx *ctx, const trt_uniforms *u) {
     return TRT_OK;
 }
 
-extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
-    if (!ctx) return TRT_ERR_INVALID;
+// One launch of the trace kernel for the frame `u` describes; with n_batch > 0 for the n_batch frames whose
+// (seed, frame_number) pairs are in ctx->d_batch (means into ctx->d_batch_cur, blended by the caller).
+static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     int rc = check_uniforms(ctx, u);
     if (rc) return rc;
     CK(cudaSetDevice(ctx->device));
@@ -402,12 +416,17 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     fp.row_map = ctx->cfg.shard_count > 1u ? ctx->d_row_map : nullptr;
     fp.pixels = ctx->d_pixels; fp.accumulation = ctx->d_accum; fp.variance = ctx->d_variance;
     fp.counters = ctx->d_counters; fp.work_counter = ctx->d_work; fp.stats = ctx->d_stats;
-    CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
-    ctx->launches = 0;
-    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    if (n_batch) {
+        if (ctx->cfg.count_work) return fail(ctx, TRT_ERR_INVALID, "frame batch on an instrumented (count_work) context");
+        fp.batch = ctx->d_batch; fp.batch_cur = ctx->d_batch_cur; fp.n_batch = n_batch;
+    } else {
+        CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
+        ctx->launches = 0;
+        CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    }
     // longest pixels first, predicted by the variance buffer of the previous frame of the same size
     static const bool no_order = [] { const char *k = getenv("TRT_B200_NO_ORDER"); return k && *k == '1'; }();
-    if (!no_order && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
+    if (!no_order && !n_batch && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
         CK(cudaMemsetAsync(ctx->d_work + 16, 0, 2 * TRT_ORDER_BUCKETS * sizeof(unsigned int), ctx->stream));
         const uint32_t ob = (fp.n_local_pixels + 255u) / 256u;
         order_count_kernel<<<ob, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width, fp.n_local_pixels, fp.base_samples,
@@ -434,7 +453,7 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
             // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)
             static const bool use_v1 = [] { const char *k = getenv("TRT_B200_KERNEL"); return k && !strcmp(k, "v1"); }();
             if (e == cudaSuccess) {
-                if (use_v1) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream, &ctx->launches);
+                if (use_v1 && !n_batch) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream, &ctx->launches);
                 else e = wave_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, scene_fits_constant(ctx->sv),
                                            ctx->stream, &ctx->launches);
             }
@@ -442,7 +461,7 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
         }
         CK(cudaGetLastError());
     }
-    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    if (!n_batch) CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     ctx->last_u = *u;
     ctx->have_frame = true;
     ctx->order_w = u->width;
@@ -450,7 +469,14 @@ extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
     return TRT_OK;
 }
 
-static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_src, uint32_t w, uint32_t rows, int mode) {
+extern "C" int trt_trace_async(trt_ctx *ctx, const trt_uniforms *u) {
+    if (!ctx) return TRT_ERR_INVALID;
+    return trace_impl(ctx, u, 0u);
+}
+
+// d_out / out_cap / h_len default to the context's stream buffer and pinned length word
+static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_src, uint32_t w, uint32_t rows, int mode,
+                           uint8_t *d_out = nullptr, size_t out_cap = 0, uint64_t *h_len = nullptr) {
     if (mode != TRT_MODE_ASCII && mode != TRT_MODE_TRUECOLOR) return fail(ctx, TRT_ERR_INVALID, "quantise: bad mode");
     const uint64_t n = (uint64_t)w * rows;
     if (n > ctx->max_pixels) return fail(ctx, TRT_ERR_INVALID, "quantise: frame exceeds the context's capacity");
@@ -458,7 +484,7 @@ static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_
     q.src = src; q.row_src = row_src; q.width = w; q.height = rows; q.mode = mode;
     q.packed = ctx->d_packed; q.block_len = ctx->d_block_len; q.block_off = ctx->d_block_off;
     q.n_blocks = (uint32_t)((n + TRT_Q_BLOCK - 1) / TRT_Q_BLOCK);
-    q.out = ctx->d_stream; q.out_cap = ctx->stream_cap;
+    q.out = d_out ? d_out : ctx->d_stream; q.out_cap = d_out ? out_cap : ctx->stream_cap;
     if (q.n_blocks) {
         quant_pack_kernel<<<q.n_blocks, TRT_Q_BLOCK, 0, ctx->stream>>>(q);
         quant_scan_kernel<<<1, 1024, 0, ctx->stream>>>(q);
@@ -469,8 +495,8 @@ static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_
         CK(cudaMemsetAsync(ctx->d_block_off, 0, sizeof(uint64_t), ctx->stream));
     }
     ctx->last_q_blocks = q.n_blocks;
-    CK(cudaMemcpyAsync(ctx->h_len, ctx->d_block_off + q.n_blocks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
-    ctx->have_stream = true;
+    CK(cudaMemcpyAsync(h_len ? h_len : ctx->h_len, ctx->d_block_off + q.n_blocks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->have_stream = d_out == nullptr;
     return TRT_OK;
 }
 
@@ -558,6 +584,134 @@ extern "C" int trt_render_frame(trt_ctx *ctx, const trt_uniforms *u, int mode, u
     size_t n = 0;
     rc = trt_read_stream(ctx, out, cap, &n);
     if (len) *len = n;
+    return rc;
+}
+
+// ---- frame batch ---------------------------------------------------------------------------------------
+// The reference's loop (lib.rs:414-560) renders the frames of a still camera one at a time, each a full GPU
+// round trip; at terminal sizes a frame is far too small to fill a B200 (80 000 serial pixel chains against
+// 151 552 resident lanes).  A batch traces n such frames -- same scene, size and camera, their own
+// (seed, frame_number) -- as ONE launch over n x pixels work items, then blends them in frame order.
+extern "C" int trt_render_frames(trt_ctx *ctx, const trt_uniforms *u, uint32_t n, int mode, int emit_all, uint8_t *out,
+                                 size_t cap, size_t *len, size_t *frame_len) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (!u || n == 0u) return fail(ctx, TRT_ERR_INVALID, "render_frames: no frames");
+    if (mode != TRT_MODE_ASCII && mode != TRT_MODE_TRUECOLOR && mode != TRT_MODE_NONE)
+        return fail(ctx, TRT_ERR_INVALID, "render_frames: bad mode");
+    if (ctx->cfg.shard_count > 1u && mode != TRT_MODE_NONE)
+        return fail(ctx, TRT_ERR_INVALID, "render_frames: a sharded context has no whole frame to emit (use TRT_MODE_NONE and gather)");
+    for (uint32_t i = 1; i < n; i++) {
+        trt_uniforms a = u[0], b = u[i];
+        a.seed = b.seed = 0u; a.frame_number = b.frame_number = 0u;
+        if (memcmp(&a, &b, sizeof(trt_uniforms)) != 0)
+            return fail(ctx, TRT_ERR_INVALID, "render_frames: the frames of a batch may differ only in seed and frame_number");
+    }
+    int rc = check_uniforms(ctx, &u[0]);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    rc = ensure_rows(ctx, u[0].width, u[0].height);
+    if (rc) return rc;
+    const size_t np = ctx->rows.size() * (size_t)u[0].width;
+    if (len) *len = 0;
+    if (np == 0) return TRT_OK;
+    const bool emit = emit_all && mode != TRT_MODE_NONE;
+    const size_t stride = (np * 26 + (size_t)u[0].height * 2 + 64 + 255) & ~(size_t)255;
+    // frames per launch: staging (16 B/pixel/frame, plus the stream when every frame is emitted) within 6 GB,
+    // and the work-item index within 31 bits
+    const size_t per_frame = np * sizeof(float4) + (emit ? stride : 0);
+    size_t chunk = (size_t(6) << 30) / per_frame;
+    if (chunk > ((size_t(1) << 31) - 1) / np) chunk = ((size_t(1) << 31) - 1) / np;
+    if (chunk < 1) chunk = 1;
+    if (chunk > n) chunk = n;
+    if (ctx->batch_cur_cap < chunk * np) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->d_batch_cur) cudaFree(ctx->d_batch_cur);
+        ctx->d_batch_cur = nullptr; ctx->batch_cur_cap = 0;
+        CK(cudaMalloc(&ctx->d_batch_cur, chunk * np * sizeof(float4)));
+        ctx->batch_cur_cap = chunk * np;
+    }
+    if (ctx->batch_cap < chunk) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->d_batch) cudaFree(ctx->d_batch);
+        ctx->d_batch = nullptr; ctx->batch_cap = 0;
+        CK(cudaMalloc(&ctx->d_batch, chunk * sizeof(uint2)));
+        ctx->batch_cap = (uint32_t)chunk;
+    }
+    if (emit) {
+        if (ctx->batch_stream_cap < chunk * stride) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            if (ctx->d_batch_stream) cudaFree(ctx->d_batch_stream);
+            ctx->d_batch_stream = nullptr; ctx->batch_stream_cap = 0;
+            CK(cudaMalloc(&ctx->d_batch_stream, chunk * stride));
+            ctx->batch_stream_cap = chunk * stride;
+        }
+        if (ctx->batch_len_cap < chunk) {
+            if (ctx->h_batch_len) cudaFreeHost(ctx->h_batch_len);
+            ctx->h_batch_len = nullptr; ctx->batch_len_cap = 0;
+            CK(cudaMallocHost(&ctx->h_batch_len, chunk * sizeof(uint64_t)));
+            ctx->batch_len_cap = chunk;
+        }
+    }
+    CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
+    ctx->launches = 0;
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    size_t off = 0;
+    std::vector<uint2> hb(chunk);
+    for (uint32_t c0 = 0; c0 < n; c0 += (uint32_t)chunk) {
+        const uint32_t m = (uint32_t)std::min<size_t>(chunk, n - c0);
+        for (uint32_t f = 0; f < m; f++) hb[f] = make_uint2(u[c0 + f].seed, u[c0 + f].frame_number);
+        CK(cudaMemcpyAsync(ctx->d_batch, hb.data(), m * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));          // hb is reused by the next chunk
+        rc = trace_impl(ctx, &u[c0], m);
+        if (rc) return rc;
+        const uint32_t *row_map = ctx->cfg.shard_count > 1u ? ctx->d_row_map : nullptr;
+        if (ctx->cfg.conv == 2u) {
+            cudaError_t e = native_blend_launch(ctx->d_batch_cur, ctx->d_batch, m, (uint32_t)np, row_map, u[0].width, ctx->d_accum,
+                                                ctx->d_pixels, ctx->stream);
+            if (e != cudaSuccess) { ctx->err = std::string("blend launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
+        } else {
+            blend_frames_kernel<0><<<((uint32_t)np + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->d_batch_cur, ctx->d_batch, m, (uint32_t)np,
+                                                                                         row_map, u[0].width, ctx->d_accum, ctx->d_pixels);
+            CK(cudaGetLastError());
+        }
+        ctx->launches += 1;
+        if (c0 + m == n) CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+        if (emit) {
+            for (uint32_t f = 0; f < m; f++) {
+                rc = launch_quantise(ctx, ctx->d_batch_cur + (size_t)f * np, nullptr, u[0].width, u[0].height, mode,
+                                     ctx->d_batch_stream + (size_t)f * stride, stride, ctx->h_batch_len + f);
+                if (rc) return rc;
+            }
+            if (c0 + m == n) CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            for (uint32_t f = 0; f < m; f++) {
+                const size_t nf = (size_t)ctx->h_batch_len[f];
+                if (frame_len) frame_len[c0 + f] = nf;
+                if (nf > stride) return fail(ctx, TRT_ERR_INVALID, "internal: stream longer than its buffer");
+                if (off + nf > cap || (!out && nf)) return fail(ctx, TRT_ERR_TOO_SMALL, "output buffer too small for the batch's streams");
+                if (nf) CK(cudaMemcpyAsync(out + off, ctx->d_batch_stream + (size_t)f * stride, nf, cudaMemcpyDeviceToHost, ctx->stream));
+                off += nf;
+            }
+        }
+    }
+    ctx->last_u = u[n - 1];
+    if (emit) {
+        CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (len) *len = off;
+        return TRT_OK;
+    }
+    if (mode == TRT_MODE_NONE) {
+        CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+        CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+        return trt_sync(ctx);
+    }
+    rc = trt_quantise_async(ctx, mode, nullptr);
+    if (rc) return rc;
+    size_t nlast = 0;
+    rc = trt_read_stream(ctx, out, cap, &nlast);
+    if (len) *len = nlast;
+    if (frame_len) { for (uint32_t i = 0; i + 1 < n; i++) frame_len[i] = 0; frame_len[n - 1] = nlast; }
     return rc;
 }
 

@@ -43,7 +43,29 @@ struct FrameParams {
     unsigned long long *counters;   // trt_counters as 19 x u64 (instrumented build only)
     unsigned int *work_counter;     // persistent kernel: next pixel to hand out
     unsigned long long *stats;      // [0] samples traced, [1] closest-hit scans (bounces) of this frame
+    // frame batch (trt_render_frames): n_batch frames that differ only in (seed, frame_number) are traced by one
+    // launch; work item = (frame, local pixel); a finished pixel stores its mean into batch_cur[frame][local pixel]
+    // and blend_frames_kernel applies the temporal blend (shader.wgsl:610-619) in frame order afterwards
+    const uint2 *batch;             // (seed, frame_number) per frame; NULL: single frame
+    float4 *batch_cur;
+    uint32_t n_batch;
 };
+
+// shader.wgsl:610-619: the temporal blend of one pixel, with explicit roundings so that every call site
+// (finish_pixel, blend_frames_kernel) produces the same bits in a given convention
+template <int CONV> __device__ __forceinline__ float4 blend_pixel(float4 a, float3 cur, uint32_t frame_number) {
+    if (frame_number == 0u) return make_float4(cur.x, cur.y, cur.z, 0.0f);
+    const float n = __uint2float_rn(frame_number + 1u);
+    float alpha;
+    if (CONV == 2) asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(alpha) : "f"(n));
+    else alpha = __fdiv_rn(1.0f, n);
+    const float oma = __fsub_rn(1.0f, alpha);
+    if (CONV == 2)
+        return make_float4(__fmaf_rn(cur.x, alpha, __fmul_rn(a.x, oma)), __fmaf_rn(cur.y, alpha, __fmul_rn(a.y, oma)),
+                           __fmaf_rn(cur.z, alpha, __fmul_rn(a.z, oma)), 0.0f);
+    return make_float4(__fadd_rn(__fmul_rn(a.x, oma), __fmul_rn(cur.x, alpha)), __fadd_rn(__fmul_rn(a.y, oma), __fmul_rn(cur.y, alpha)),
+                       __fadd_rn(__fmul_rn(a.z, oma), __fmul_rn(cur.z, alpha)), 0.0f);
+}
 
 __device__ __forceinline__ float3 f3(float x, float y, float z) { return make_float3(x, y, z); }
 __device__ __forceinline__ float3 xyz(float4 v) { return make_float3(v.x, v.y, v.z); }

@@ -142,6 +142,30 @@ static __global__ void order_scatter_kernel(const trt_variance *variance, const 
     if (live) order[start[b] + base[b] + rank] = lp;
 }
 
+// ---- frame batch: temporal blend in frame order (shader.wgsl:610-619) ------------------------------------
+// cur[f][lp] holds frame f's pixel mean (finish_pixel); one thread per local pixel walks the frames in order and
+// applies exactly the blend a sequence of single-frame launches applies, so the accumulation after the batch is
+// bit-identical to theirs.  The running value is written back over cur[f][lp]: frame f's displayed pixels (:620),
+// which is what the quantiser reads when every frame's byte stream is wanted.
+template <int CONV>
+static __global__ void blend_frames_kernel(float4 *cur, const uint2 *batch, uint32_t n_batch, uint32_t n_local_pixels,
+                                           const uint32_t *row_map, uint32_t width, float4 *accumulation, float4 *pixels) {
+    const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
+    if (lp >= n_local_pixels) return;
+    const uint32_t lr = lp / width, x = lp - lr * width;
+    const uint32_t y = row_map ? row_map[lr] : lr;
+    const size_t index = (size_t)y * width + x;
+    float4 a = accumulation[index];
+    for (uint32_t f = 0; f < n_batch; f++) {
+        const size_t s = (size_t)f * n_local_pixels + lp;
+        const float4 c = cur[s];
+        a = blend_pixel<CONV>(a, make_float3(c.x, c.y, c.z), __ldg(&batch[f]).y);
+        cur[s] = a;
+    }
+    accumulation[index] = a;
+    pixels[index] = a;
+}
+
 // pack the rows this shard owns contiguously (local row order) for the NCCL gather
 static __global__ void pack_rows_kernel(const float4 *src, float4 *dst, const uint32_t *row_map, uint32_t width,
                                  uint32_t n_local_pixels) {

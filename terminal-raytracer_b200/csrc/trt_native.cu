@@ -50,7 +50,8 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         cudaFuncSetAttribute(trace_native_kernel<SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         carveout_set = true;
     }
-    const uint32_t want = (fp.n_local_pixels + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
+    const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
+    const uint32_t want = (n_work + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
     const uint32_t cap = (uint32_t)sm_count * TRT_NV_CTAS_PER_SM;
     const uint32_t blocks = want < cap ? want : cap;
     // the reference's default scene shape (3 spheres, 6 axis-aligned walls in y y x x z z order, 2 triangles)
@@ -67,13 +68,21 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         else if (constant) trace_native_kernel<SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
         else trace_native_kernel<SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
     } else {
-        const uint32_t wwant = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
+        const uint32_t wwant = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
         const uint32_t wcap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
         const uint32_t wblocks = wwant < wcap ? wwant : wcap;
         if (constant) trace_wave_kernel<2, SrcConst><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
         else trace_wave_kernel<2, SrcGlobal><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
     }
     *launches += 1;
+    return cudaGetLastError();
+}
+
+// conv 2 instance of the frame-batch blend (same translation unit, hence same flags, as finish_pixel<2>)
+cudaError_t native_blend_launch(float4 *cur, const uint2 *batch, uint32_t n_batch, uint32_t n_local_pixels, const uint32_t *row_map,
+                                uint32_t width, float4 *accumulation, float4 *pixels, cudaStream_t stream) {
+    blend_frames_kernel<2><<<(n_local_pixels + 255u) / 256u, 256, 0, stream>>>(cur, batch, n_batch, n_local_pixels, row_map, width,
+                                                                              accumulation, pixels);
     return cudaGetLastError();
 }
 

@@ -66,7 +66,8 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
     int sp_k = -1;                               // >= 0: the warp is resolving the oldest entries against light sp_k
     uint32_t pend = 0;                           // entries this lane has posted so far
     int mode = NM_NEED_PIXEL;
-    uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0;
+    uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0, fslot = 0;
+    const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     bool extra_phase = false;
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
     float3 att = f3(1, 1, 1), acc = f3(0, 0, 0);
@@ -102,7 +103,7 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
             }
             if (finished) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
-                tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value);
+                tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, fslot);
                 mode = NM_NEED_PIXEL;
             } else {
                 new_ray = true;
@@ -118,13 +119,21 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
             base = __shfl_sync(0xffffffffu, base, leader);
             if (mode == NM_NEED_PIXEL) {
                 const uint32_t slot = base + __popc(need & lt_mask);
-                if (slot < fp.n_local_pixels) {
-                    const uint32_t lp = fp.order ? fp.order[slot] : slot;
+                if (slot < n_work) {
+                    uint32_t ls = slot, seed = fp.seed, frame_number = fp.frame_number;
+                    if (fp.batch) {                              // frame batch: work item = (frame, local pixel)
+                        const uint32_t f = slot / fp.n_local_pixels;
+                        ls = slot - f * fp.n_local_pixels;
+                        const uint2 b = __ldg(&fp.batch[f]);
+                        seed = b.x; frame_number = b.y;
+                    }
+                    const uint32_t lp = fp.order ? fp.order[ls] : ls;
                     const uint32_t lr = lp / fp.width;
                     const uint32_t x = lp - lr * fp.width;
                     const uint32_t y = fp.row_map ? fp.row_map[lr] : lr;
                     xy = x | (y << 16);
-                    rng = (y * fp.width + x) * 1973u + fp.seed * 9277u + fp.frame_number * 12345u;   // shader.wgsl:507
+                    fslot = slot - ls + lp;
+                    rng = (y * fp.width + x) * 1973u + seed * 9277u + frame_number * 12345u;   // shader.wgsl:507
                     pixel_color = f3(0, 0, 0);
                     sq_sum = f3(0, 0, 0);
                     si = 0;

@@ -685,23 +685,24 @@ struct Tracer {
         finish_pixel(x, y, pixel_color, variance_value);
     }
 
-    // shader.wgsl:605-621: variance store, temporal accumulation, pixel store (one float4 per buffer)
-    __device__ __forceinline__ void finish_pixel(uint32_t x, uint32_t y, float3 pixel_color, float variance_value) {
+    // shader.wgsl:605-621: variance store, temporal accumulation, pixel store (one float4 per buffer).
+    // In a frame batch (fp.batch) the pixel's mean goes to the batch buffer instead (fslot = frame * n_local_pixels
+    // + local pixel) and only the last frame of the batch leaves its variance behind, as sequential frames would.
+    __device__ __forceinline__ void finish_pixel(uint32_t x, uint32_t y, float3 pixel_color, float variance_value, uint32_t fslot = 0u) {
         size_t index = (size_t)y * fp.width + x;
         trt_variance vb;
         vb.variance = variance_value;
         vb.sample_count = fp.base_samples;
-        fp.variance[index] = vb;
         float3 cur = V::divs(pixel_color, fp.spp_f);
-        float4 out;
-        if (fp.frame_number == 0u) {
-            out = make_float4(cur.x, cur.y, cur.z, 0.0f);
-        } else {
-            float alpha = 1.0f / __uint2float_rn(fp.frame_number + 1u);
-            float4 a = fp.accumulation[index];
-            float3 r = V::add(V::scale(xyz(a), 1.0f - alpha), V::scale(cur, alpha));
-            out = make_float4(r.x, r.y, r.z, 0.0f);
+        if (fp.batch) {
+            fp.batch_cur[fslot] = make_float4(cur.x, cur.y, cur.z, 0.0f);
+            if (fslot >= (fp.n_batch - 1u) * fp.n_local_pixels) fp.variance[index] = vb;
+            return;
         }
+        fp.variance[index] = vb;
+        float4 a = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (fp.frame_number != 0u) a = fp.accumulation[index];
+        const float4 out = blend_pixel<CONV>(a, cur, fp.frame_number);
         fp.accumulation[index] = out;
         fp.pixels[index] = out;
     }

@@ -43,7 +43,8 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
     const unsigned lt_mask = (1u << lane) - 1u;
 
     int mode = WM_NEED_PIXEL;
-    uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0;
+    uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0, fslot = 0;
+    const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     bool extra_phase = false;
     float variance_value = 0.0f;
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
@@ -66,13 +67,21 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
             base = __shfl_sync(0xffffffffu, base, leader);
             if (mode == WM_NEED_PIXEL) {
                 const uint32_t slot = base + __popc(need & lt_mask);
-                if (slot < fp.n_local_pixels) {
-                    const uint32_t lp = fp.order ? fp.order[slot] : slot;
+                if (slot < n_work) {
+                    uint32_t ls = slot, seed = fp.seed, frame_number = fp.frame_number;
+                    if (fp.batch) {                              // frame batch: work item = (frame, local pixel)
+                        const uint32_t f = slot / fp.n_local_pixels;
+                        ls = slot - f * fp.n_local_pixels;
+                        const uint2 b = __ldg(&fp.batch[f]);
+                        seed = b.x; frame_number = b.y;
+                    }
+                    const uint32_t lp = fp.order ? fp.order[ls] : ls;
                     const uint32_t lr = lp / fp.width;
                     const uint32_t x = lp - lr * fp.width;
                     const uint32_t y = fp.row_map ? fp.row_map[lr] : lr;
                     xy = x | (y << 16);
-                    rng = (y * fp.width + x) * 1973u + fp.seed * 9277u + fp.frame_number * 12345u;   // shader.wgsl:507
+                    fslot = slot - ls + lp;
+                    rng = (y * fp.width + x) * 1973u + seed * 9277u + frame_number * 12345u;   // shader.wgsl:507
                     pixel_color = f3(0, 0, 0);
                     sq_sum = f3(0, 0, 0);
                     si = 0;
@@ -244,7 +253,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
             }
             if (finished) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
-                tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value);
+                tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, fslot);
                 mode = WM_NEED_PIXEL;
             } else {                                              // next sample (shader.wgsl:517 / :565)
                 rng = pcg_hash(rng + si * 5096u);
@@ -265,7 +274,8 @@ static inline cudaError_t wave_trace_launch(const SceneView &sv, const LightView
                                             int sm_count, bool small, cudaStream_t stream, uint32_t *launches) {
     cudaError_t e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
-    const uint32_t want = (fp.n_local_pixels + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
+    const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
+    const uint32_t want = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
     const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
     const uint32_t blocks = want < cap ? want : cap;
     if (small) {
