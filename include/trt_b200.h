@@ -247,6 +247,9 @@ typedef struct trt_run_options {
     int32_t device;
     uint32_t conv;
     uint32_t quiet;               /* suppress the status line */
+    uint32_t batch_frames;        /* > 1: while the camera is still, render this many frames per GPU round trip
+                                   * (trt_render_frames) and show the last one; 0 / 1: one frame per round trip as
+                                   * the reference does */
 } trt_run_options;
 int trt_run(int full_color, int verbose, const char *scene_path_or_null, const trt_run_options *opts);
 

@@ -91,7 +91,7 @@ class SceneInfo(C.Structure):
 class RunOptions(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("frames", C.c_uint32), ("seed", C.c_uint32),
                 ("has_seed", C.c_uint32), ("keys", C.c_char_p), ("out_path", C.c_char_p), ("device", C.c_int32),
-                ("conv", C.c_uint32), ("quiet", C.c_uint32)]
+                ("conv", C.c_uint32), ("quiet", C.c_uint32), ("batch_frames", C.c_uint32)]
 
 
 assert C.sizeof(Vec3) == 16 and C.sizeof(Primitive) == 180 and C.sizeof(Uniforms) == 160
@@ -450,7 +450,7 @@ def measure_fp32_peak(device=0):
 
 def run(full_color: bool, verbose: bool, scene_path: str | None, **opts) -> int:
     """The reference's `run(full_color, verbose, scene_path)` (lib.rs:100); keyword extensions map to
-    trt_run_options (width, height, frames, seed, keys, out_path, device, conv, quiet)."""
+    trt_run_options (width, height, frames, seed, keys, out_path, device, conv, quiet, batch_frames)."""
     o = RunOptions()
     for k, v in opts.items():
         if k == "seed":

@@ -14,6 +14,7 @@ int main(int argc, char **argv) {
     const char *path = nullptr;
     long threads = -1;
     trt_run_options o{};
+    o.conv = TRT_CONV_NATIVE;          // the production arithmetic; --strict / --fused select the bit-exact builds
     for (int i = 1; i < argc; i++) {
         const std::string a = argv[i];
         const char *next = i + 1 < argc ? argv[i + 1] : nullptr;
@@ -29,6 +30,9 @@ int main(int argc, char **argv) {
         else if (a == "--out" && next) o.out_path = next;
         else if (a == "--device" && next) o.device = (int32_t)strtol(next, nullptr, 10);
         else if (a == "--fused") o.conv = TRT_CONV_FUSED;
+        else if (a == "--strict") o.conv = TRT_CONV_AS_WRITTEN;
+        else if (a == "--native") o.conv = TRT_CONV_NATIVE;
+        else if (a == "--batch" && next) o.batch_frames = (uint32_t)strtoul(next, nullptr, 10);
         else if (a == "--quiet") o.quiet = 1;
     }
     if (threads <= 0) {                                                    // main.rs:18-19

@@ -123,6 +123,7 @@ extern "C" int trt_run(int full_color, int verbose, const char *scene_path, cons
     if (tty) { raw.enter(); fputs("\x1b[?25l\x1b[2J\x1b[1;1H", sink); fflush(sink); }   // lib.rs:355-368
 
     std::random_device rd;
+    std::vector<trt_uniforms> batch_u;
     uint32_t frame_count = 0, rendered = 0;
     bool camera_moved = true;
     std::deque<double> frame_times;                              // lib.rs:362-364
@@ -144,16 +145,23 @@ extern "C" int trt_run(int full_color, int verbose, const char *scene_path, cons
         if (rendered >= frame_budget) break;
 
         if (frame_count < info.frames_to_accumulate) {           // lib.rs:415
-            trt_uniforms u;
-            const uint32_t seed = opts.has_seed ? opts.seed + 0x9E3779B9u * rendered : (uint32_t)rd() + frame_count;   // lib.rs:423
-            trt_fill_uniforms(scene, &cam, seed, camera_moved ? 0u : frame_count, &u);                                 // lib.rs:424
+            // frames of this GPU round trip: 1 as in the reference, or a batch while the camera is still (extension)
+            uint32_t k = opts.batch_frames > 1u ? opts.batch_frames : 1u;
+            if (k > info.frames_to_accumulate - frame_count) k = info.frames_to_accumulate - frame_count;
+            if (k > frame_budget - rendered) k = frame_budget - rendered;
+            batch_u.resize(k);
+            for (uint32_t j = 0; j < k; j++) {
+                const uint32_t seed = opts.has_seed ? opts.seed + 0x9E3779B9u * (rendered + j) : (uint32_t)rd() + frame_count + j;   // lib.rs:423
+                trt_fill_uniforms(scene, &cam, seed, camera_moved && j == 0 ? 0u : frame_count + j, &batch_u[j]);                  // lib.rs:424
+            }
             size_t len = 0;
             auto t_gpu = clk::now();
-            status = trt_render_frame(ctx, &u, mode, bytes, cap, &len);
+            status = k == 1u ? trt_render_frame(ctx, &batch_u[0], mode, bytes, cap, &len)
+                             : trt_render_frames(ctx, batch_u.data(), k, mode, 0, bytes, cap, &len, nullptr);
             if (status != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); break; }
             const double gpu_ms = ms_since(t_gpu);
-            frame_count++;                                       // lib.rs:457
-            rendered++;
+            frame_count += k;                                    // lib.rs:457
+            rendered += k;
             auto now = clk::now();
             frame_times.push_back(std::chrono::duration<double>(now - last_frame).count());
             last_frame = now;
