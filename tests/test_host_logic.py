@@ -30,6 +30,27 @@ def test_library_exports_every_declared_symbol(pkg):
     assert declared == set(pkg.api.SYMBOLS), declared ^ set(pkg.api.SYMBOLS)
 
 
+def test_rust_binding_declares_every_symbol():
+    """bindings/rust/trt-b200-sys (source only: no Rust toolchain in this image) must declare every entry point
+    of the header, with the same number of parameters."""
+    hdr = open(os.path.join(ROOT, "include", "trt_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    rs = open(os.path.join(ROOT, "bindings", "rust", "trt-b200-sys", "src", "lib.rs")).read()
+    rs = re.sub(r"//.*", "", rs)
+    ext = rs[rs.index('extern "C" {'):]
+    ext = ext[:ext.index("\n}\n")]
+    rust = {m.group(1): m.group(2) for m in re.finditer(r"pub fn (trt_[a-z0-9_]+)\s*\((.*?)\)\s*(?:->[^;]*)?;", ext, flags=re.S)}
+    cdecl = {m.group(1): m.group(2) for m in re.finditer(r"\b(trt_[a-z0-9_]+)\s*\(([^)]*)\)\s*;", hdr)}
+    assert set(cdecl) == set(rust), set(cdecl) ^ set(rust)
+
+    def arity(params):
+        params = params.strip()
+        return 0 if params in ("", "void") else params.count(",") + 1
+
+    bad = [n for n in cdecl if arity(cdecl[n]) != arity(rust[n])]
+    assert not bad, bad
+
+
 def test_wire_struct_sizes(pkg):
     import ctypes as C
     a = pkg.api
