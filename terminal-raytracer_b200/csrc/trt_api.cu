@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <cmath>
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -36,6 +37,8 @@ struct trt_ctx {
     float4 *d_geom = nullptr;          // ga|gb|gc|gn|mc|me, each cap_prims long
     uint8_t *d_type = nullptr;
     int4 *d_runs = nullptr;
+    int4 *d_tiles = nullptr;           // (type, first, count, -) per tile of the cooperative scan
+    size_t cap_tiles = 0;
     int4 *d_lights = nullptr;
     int *d_light_prim = nullptr;
     float4 *d_lgeom = nullptr;         // la|lb|lc|ln|le, each cap_lights long
@@ -109,7 +112,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
+    void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_tiles, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
                     ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
                     ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream};
     for (void *p : ptrs) if (p) cudaFree(p);
@@ -268,6 +271,10 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
         }
         ctx->small = sm;
     }
+    // tiles of the CTA-cooperative scan: at most TRT_TILE consecutive primitives of one run, in scan order
+    std::vector<int4> tiles;
+    for (const int4 &r : runs)
+        for (int t0 = r.y; t0 < r.z; t0 += TRT_TILE) tiles.push_back(make_int4(r.x, t0, std::min(TRT_TILE, r.z - t0), 0));
     const uint32_t n_lights = (uint32_t)light_prim.size(), n_runs = (uint32_t)runs.size();
     CK(cudaStreamSynchronize(ctx->stream));
     if (count > ctx->cap_prims) {
@@ -295,6 +302,15 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
         CK(cudaMalloc(&ctx->d_runs, (size_t)cap * sizeof(int4)));
         ctx->cap_runs = cap;
     }
+    if (tiles.size() > ctx->cap_tiles || !ctx->d_tiles) {
+        if (ctx->d_tiles) cudaFree(ctx->d_tiles);
+        ctx->d_tiles = nullptr; ctx->cap_tiles = 0;
+        const size_t cap = tiles.size() < 16 ? 16 : tiles.size();
+        CK(cudaMalloc(&ctx->d_tiles, cap * sizeof(int4)));
+        ctx->cap_tiles = cap;
+    }
+    if (!tiles.empty())
+        CK(cudaMemcpyAsync(ctx->d_tiles, tiles.data(), tiles.size() * sizeof(int4), cudaMemcpyHostToDevice, ctx->stream));
     if (count) {
         CK(cudaMemcpyAsync(ctx->d_aos, prims, (size_t)count * sizeof(trt_primitive), cudaMemcpyHostToDevice, ctx->stream));
         CK(cudaMemcpyAsync(ctx->d_type, types.data(), count, cudaMemcpyHostToDevice, ctx->stream));
@@ -322,6 +338,7 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     ctx->sv.ga = rp.ga; ctx->sv.gb = rp.gb; ctx->sv.gc = rp.gc; ctx->sv.gn = rp.gn; ctx->sv.mc = rp.mc; ctx->sv.me = rp.me;
     ctx->sv.type = ctx->d_type; ctx->sv.runs = ctx->d_runs; ctx->sv.lights = ctx->d_lights;
     ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;
+    ctx->sv.tiles = ctx->d_tiles; ctx->sv.n_tiles = (int)tiles.size();
     ctx->lv.la = rp.la; ctx->lv.lb = rp.lb; ctx->lv.lc = rp.lc; ctx->lv.ln = rp.ln; ctx->lv.le = rp.le;
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->have_scene = true;

@@ -25,7 +25,12 @@ struct SceneView {
     const int4 *runs;           // (type, begin, end, -) maximal runs of equal type, in scan order
     const int4 *lights;         // (prim index, type, area as float bits, -) emissive spheres/triangles in scan order
     int n_prims, n_runs, n_lights;
+    // tiles of at most TRT_TILE consecutive primitives of one run, in scan order: (type, first index, count, -);
+    // the CTA-cooperative scan of large scenes stages one tile at a time in shared memory (trt_trace.cuh)
+    const int4 *tiles;
+    int n_tiles;
 };
+#define TRT_TILE 128
 
 #define TRT_CONST_PRIMS 256     // scenes up to this size are also mirrored in __constant__ memory
 

@@ -42,12 +42,14 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     static const char *force = getenv("TRT_B200_NATIVE");
     const bool force_wave = force && !strcmp(force, "wave");
     const bool force_generic = force && !strcmp(force, "generic");
+    const bool force_untiled = force && !strcmp(force, "untiled");     // large scenes: every warp scans on its own
     const bool constant = scene_fits_constant(sv);
     static bool carveout_set = false;
     if (!carveout_set) {
         cudaFuncSetAttribute(trace_native_kernel<SrcConst, ShapeCornell>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<SrcTiled, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         carveout_set = true;
     }
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
@@ -66,6 +68,10 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
         if (cornell) trace_native_kernel<SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
         else if (constant) trace_native_kernel<SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else if (sv.n_tiles > 0 && !force_untiled) {
+            const uint32_t tcap = (uint32_t)sm_count * SrcTiled::kCtasPerSm;
+            trace_native_kernel<SrcTiled, ShapeAny><<<want < tcap ? want : tcap, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        }
         else trace_native_kernel<SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
     } else {
         const uint32_t wwant = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;

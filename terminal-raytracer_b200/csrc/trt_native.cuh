@@ -46,7 +46,7 @@ enum { NM_ACTIVE = 0, NM_WAIT = 1, NM_NEED_PIXEL = 2, NM_DONE = 3 };
 enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ_META, DQ_FIELDS };
 
 template <class SRC, class SHAPE>
-__global__ void __launch_bounds__(TRT_NV_THREADS, TRT_NV_CTAS_PER_SM)
+__global__ void __launch_bounds__(TRT_NV_THREADS, SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
 trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
     typedef M<2> V;
     Counters<false> cn;
@@ -54,6 +54,7 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
     __shared__ float s_ring[TRT_NV_THREADS / 32][DQ_FIELDS][TRT_NV_RING];
     __shared__ float s_late[3][TRT_NV_THREADS];
     __shared__ unsigned s_res[TRT_NV_THREADS];
+    __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
     const unsigned tid = threadIdx.x, lane = tid & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     float (*ring)[TRT_NV_RING] = s_ring[tid >> 5];
@@ -154,7 +155,8 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
             depth = 0;
             mode = NM_ACTIVE;
         }
-        if (__all_sync(0xffffffffu, mode == NM_DONE)) break;
+        // (the cooperative scan of SrcTiled needs every warp of the CTA in every iteration: leave together)
+        if (SRC::kTiled ? __syncthreads_and(mode == NM_DONE) : __all_sync(0xffffffffu, mode == NM_DONE)) break;
 
         // ---- this iteration's scan: one light of the queued hits (when enough have queued up, or lanes are
         // waiting for them) or every lane's own closest-hit ray ------------------------------------------------------
@@ -235,7 +237,11 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
         }
         int best = -1;
         float t_hit = -1.0f;
-        if (fp.max_depth != 0u) t_hit = small ? tr.template scan_small_native<SHAPE>(qo, qd, qt, best) : tr.scan_native(qo, qd, qt, best);
+        if (fp.max_depth != 0u) {
+            if (small) t_hit = tr.template scan_small_native<SHAPE>(qo, qd, qt, best);
+            else if (SRC::kTiled) t_hit = tr.scan_native_tiled(qo, qd, mode == NM_ACTIVE || spass ? qt : -1.0f, best, s_tile, spass);
+            else t_hit = tr.scan_native(qo, qd, qt, best);
+        }
 
         if (spass) {                                              // shader.wgsl:402-431 for the queued hits
             if (qvalid) {
