@@ -45,6 +45,47 @@ enum { NM_ACTIVE = 0, NM_WAIT = 1, NM_NEED_PIXEL = 2, NM_DONE = 3 };
 // the light loop (advanced light by light while the entry is being resolved), meta = owner thread | mask << 8
 enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ_META, DQ_FIELDS };
 
+// The sample of light k for a queued hit (shader.wgsl:350-429): sample point from the two draws (:352-389), the
+// two cosines (:403-404) and, when both are positive, the shadow ray (:394-399) and the clamped contribution
+// (:408-429).  Returns whether the shadow ray is needed.
+template <class TR>
+__device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, float3 C, float r1, float r2, float3 &qo, float3 &qd,
+                                           float &qt, float3 &qc) {
+    typedef M<2> V;
+    const float4 a = tr.src.la(k);
+    const float4 nl = tr.src.ln(k);
+    const float4 em = tr.src.le(k);
+    float3 light_vec;
+    float sl;
+    if (__float_as_int(em.w) == 0) {                  // uniform sphere sampling :352-369
+        const float cos_theta = 1.0f - 2.0f * r1;
+        const float sin_theta = sqrt_native(1.0f - cos_theta * cos_theta);
+        float sp, cp;
+        sincos_turn<2>(r2, sp, cp);
+        const float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
+        light_vec = V::sub(V::axpy(xyz(a), local, a.w), P);
+        sl = V::dot(local, light_vec);
+    } else {                                          // uniform triangle sampling :370-389
+        const float sqrt_r1 = sqrt_native(r1);
+        const float u = 1.0f - sqrt_r1;
+        const float v = r2 * sqrt_r1;
+        const float3 light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(tr.src.lb(k)), u, xyz(tr.src.lc(k)), v);
+        light_vec = V::sub(light_point, P);
+        sl = V::dot(xyz(nl), light_vec);
+    }
+    const float ss = V::dot(N, light_vec);
+    if (!(ss > 0.0f && sl < 0.0f)) return false;      // both cosines must be positive (:403-404)
+    const float d2 = V::dot(light_vec, light_vec);
+    const float inv_len = rsqrt_native(d2);
+    qo = V::axpy(P, N, 0.001f);                       // :394-399
+    qd = V::scale(light_vec, inv_len);
+    qt = d2 * inv_len - 0.001f;
+    const float geometric = ((ss * inv_len) * -(sl * inv_len)) * rcp_native(d2);
+    const float3 cc = V::mulv(V::scale(C, 0.31830988618f), V::scale(xyz(em), geometric * nl.w));
+    qc = f3(fminf(cc.x, 10.0f), fminf(cc.y, 10.0f), fminf(cc.z, 10.0f));
+    return true;
+}
+
 template <class SRC, class SHAPE>
 __global__ void __launch_bounds__(TRT_NV_THREADS, SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
 trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
@@ -55,16 +96,23 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
     __shared__ float s_late[3][TRT_NV_THREADS];
     __shared__ unsigned s_res[TRT_NV_THREADS];
     __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
+    // SrcTiled: second FIFO, of ready shadow rays (origin, direction, contribution, t_max in DQ_RNG, owner in DQ_META)
+    __shared__ float s_rays[SRC::kTiled ? TRT_NV_THREADS / 32 : 1][DQ_FIELDS][SRC::kTiled ? TRT_NV_RING : 1];
     const unsigned tid = threadIdx.x, lane = tid & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     float (*ring)[TRT_NV_RING] = s_ring[tid >> 5];
+    float (*rays)[SRC::kTiled ? TRT_NV_RING : 1] = s_rays[SRC::kTiled ? tid >> 5 : 0];
     volatile float *late_x = &s_late[0][tid], *late_y = &s_late[1][tid], *late_z = &s_late[2][tid];
     volatile unsigned *res = &s_res[tid];
     *late_x = 0.0f; *late_y = 0.0f; *late_z = 0.0f; *res = 0u;
     __syncwarp();
 
     uint32_t head = 0, tail = 0;                 // FIFO counters, identical in every lane of the warp
-    int sp_k = -1;                               // >= 0: the warp is resolving the oldest entries against light sp_k
+    uint32_t rhead = 0, rtail = 0;               // SrcTiled: the FIFO of ready shadow rays
+    // small scenes: >= 0 while the warp resolves the oldest entries against light sp_k; SrcTiled: the next light the
+    // oldest batch of hits is expanded against
+    int sp_k = SRC::kTiled ? 0 : -1;
+    uint32_t sp_n = 0;                           // SrcTiled: number of hits in the batch being expanded
     uint32_t pend = 0;                           // entries this lane has posted so far
     int mode = NM_NEED_PIXEL;
     uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0, fslot = 0;
@@ -158,80 +206,126 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
         // (the cooperative scan of SrcTiled needs every warp of the CTA in every iteration: leave together)
         if (SRC::kTiled ? __syncthreads_and(mode == NM_DONE) : __all_sync(0xffffffffu, mode == NM_DONE)) break;
 
-        // ---- this iteration's scan: one light of the queued hits (when enough have queued up, or lanes are
-        // waiting for them) or every lane's own closest-hit ray ------------------------------------------------------
-        const uint32_t cnt = tail - head;
-        if (sp_k < 0 && cnt > 0u) {
-            const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
-            const unsigned m_wait = __ballot_sync(0xffffffffu, mode == NM_WAIT);
-            if (cnt >= 32u || cnt + 2u * __popc(m_wait) >= 32u || !m_active) sp_k = 0;
-        }
-        const bool spass = sp_k >= 0;
+        // ---- this iteration's scan: queued light samples (when enough have queued up, or lanes are waiting for
+        // them) or every lane's own closest-hit ray -------------------------------------------------------------------
+        bool spass = false, qvalid = false, qneed = false;
         float3 qo = ro, qd = rd, qc = f3(0, 0, 0);
         float qt = 1e10f;
         unsigned qowner = 0, qrest = 0;
-        uint32_t qrng = 0;
-        bool qneed = false;
-        const uint32_t qn = cnt < 32u ? cnt : 32u;
+        uint32_t qrng = 0, qn = 0;
         const uint32_t qe = (head + lane) & (TRT_NV_RING - 1u);
-        const bool qvalid = spass && lane < qn;
-        if (spass) {
-            unsigned lmask = 0;
-            if (qvalid) {
-                const unsigned meta = __float_as_uint(ring[DQ_META][qe]);
-                qowner = meta & 0xffu;
-                lmask = meta >> 8;
-                qrng = __float_as_uint(ring[DQ_RNG][qe]);
-            }
-            const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
-            int k = sp_k;
-            while (!((uni >> k) & 1u)) {                          // lights no queued hit can see: only their draws
-                qrng = pcg_hash(pcg_hash(qrng));
-                k++;
-            }
-            sp_k = k;
-            qrest = uni >> (k + 1);
-            const uint32_t s1 = pcg_hash(qrng);                   // the two draws of :350-351 / :371-372, in order
-            qrng = pcg_hash(s1);
-            qt = -1.0f;                                           // nothing to find unless the sample is needed
-            if ((lmask >> k) & 1u) {
-                const float r1 = __uint2float_rn(s1) * 2.3283064365386963e-10f;
-                const float r2 = __uint2float_rn(qrng) * 2.3283064365386963e-10f;
-                const float3 P = f3(ring[DQ_PX][qe], ring[DQ_PY][qe], ring[DQ_PZ][qe]);
-                const float3 N = f3(ring[DQ_NX][qe], ring[DQ_NY][qe], ring[DQ_NZ][qe]);
-                const float4 a = tr.src.la(k);
-                const float4 nl = tr.src.ln(k);
-                const float4 em = tr.src.le(k);
-                float3 light_vec;
-                float sl;
-                if (__float_as_int(em.w) == 0) {                  // uniform sphere sampling :352-369
-                    const float cos_theta = 1.0f - 2.0f * r1;
-                    const float sin_theta = sqrt_native(1.0f - cos_theta * cos_theta);
-                    float sp, cp;
-                    sincos_turn<2>(r2, sp, cp);
-                    const float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
-                    light_vec = V::sub(V::axpy(xyz(a), local, a.w), P);
-                    sl = V::dot(local, light_vec);
-                } else {                                          // uniform triangle sampling :370-389
-                    const float sqrt_r1 = sqrt_native(r1);
-                    const float u = 1.0f - sqrt_r1;
-                    const float v = r2 * sqrt_r1;
-                    const float3 light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(tr.src.lb(k)), u, xyz(tr.src.lc(k)), v);
-                    light_vec = V::sub(light_point, P);
-                    sl = V::dot(xyz(nl), light_vec);
+        if (SRC::kTiled) {
+            // Large scenes: a scan costs ~0.5 M instructions per warp, so only NEEDED shadow rays may occupy a scan
+            // slot.  Stage 1 (no scan): the queued hits are expanded light by light into a second FIFO of ready
+            // shadow rays; a sample that is not needed (a cosine <= 0) is resolved on the spot.  Stage 2: 32 queued
+            // rays share one scan.
+            const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
+            const uint32_t waiters2 = 2u * __popc(__ballot_sync(0xffffffffu, mode == NM_WAIT));
+            uint32_t cnt = tail - head, rcnt = rtail - rhead;
+            while (cnt > 0u && rcnt < 32u && (cnt >= 32u || !m_active || cnt + waiters2 >= 32u)) {
+                if (sp_k == 0) sp_n = cnt < 32u ? cnt : 32u;      // a batch keeps its size while hits queue up behind it
+                const uint32_t en = sp_n;
+                const uint32_t ee = (head + lane) & (TRT_NV_RING - 1u);
+                unsigned lmask = 0, owner = 0;
+                uint32_t erng = 0;
+                if (lane < en) {
+                    const unsigned meta = __float_as_uint(ring[DQ_META][ee]);
+                    owner = meta & 0xffu;
+                    lmask = meta >> 8;
+                    erng = __float_as_uint(ring[DQ_RNG][ee]);
                 }
-                const float ss = V::dot(N, light_vec);
-                if (ss > 0.0f && sl < 0.0f) {                     // both cosines positive (:403-404)
+                const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
+                int k = sp_k;
+                while (!((uni >> k) & 1u)) {                      // lights no queued hit can see: only their draws
+                    erng = pcg_hash(pcg_hash(erng));
+                    k++;
+                }
+                const uint32_t s1 = pcg_hash(erng);               // the two draws of :350-351 / :371-372, in order
+                erng = pcg_hash(s1);
+                bool needed = false;
+                float3 so = f3(0, 0, 0), sd = f3(0, 0, 1), scn = f3(0, 0, 0);
+                float st = 0.0f;
+                if ((lmask >> k) & 1u) {
+                    const float3 P = f3(ring[DQ_PX][ee], ring[DQ_PY][ee], ring[DQ_PZ][ee]);
+                    const float3 N = f3(ring[DQ_NX][ee], ring[DQ_NY][ee], ring[DQ_NZ][ee]);
+                    const float3 C = f3(ring[DQ_CX][ee], ring[DQ_CY][ee], ring[DQ_CZ][ee]);
+                    needed = nee_sample(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
+                                        __uint2float_rn(erng) * 2.3283064365386963e-10f, so, sd, st, scn);
+                    if (!needed) atomicAdd(&s_res[owner], 1u);
+                }
+                const unsigned mn = __ballot_sync(0xffffffffu, needed);
+                if (needed) {
+                    const uint32_t e = (rtail + __popc(mn & lt_mask)) & (TRT_NV_RING - 1u);
+                    rays[DQ_PX][e] = so.x; rays[DQ_PY][e] = so.y; rays[DQ_PZ][e] = so.z;
+                    rays[DQ_NX][e] = sd.x; rays[DQ_NY][e] = sd.y; rays[DQ_NZ][e] = sd.z;
+                    rays[DQ_CX][e] = scn.x; rays[DQ_CY][e] = scn.y; rays[DQ_CZ][e] = scn.z;
+                    rays[DQ_RNG][e] = st;
+                    rays[DQ_META][e] = __uint_as_float(owner);
+                }
+                rtail += __popc(mn);
+                if (uni >> (k + 1)) {                             // more lights for this batch of hits
+                    sp_k = k + 1;
+                    if (lane < en) ring[DQ_RNG][ee] = __uint_as_float(erng);
+                } else {
+                    sp_k = 0;
+                    head += en;
+                }
+                __syncwarp();
+                cnt = tail - head;
+                rcnt = rtail - rhead;
+            }
+            spass = rcnt >= 32u || (rcnt > 0u && (!m_active || rcnt + waiters2 >= 32u));
+            if (spass) {
+                qn = rcnt < 32u ? rcnt : 32u;
+                qvalid = lane < qn;
+                qt = -1.0f;
+                if (qvalid) {
+                    const uint32_t e = (rhead + lane) & (TRT_NV_RING - 1u);
+                    qo = f3(rays[DQ_PX][e], rays[DQ_PY][e], rays[DQ_PZ][e]);
+                    qd = f3(rays[DQ_NX][e], rays[DQ_NY][e], rays[DQ_NZ][e]);
+                    qc = f3(rays[DQ_CX][e], rays[DQ_CY][e], rays[DQ_CZ][e]);
+                    qt = rays[DQ_RNG][e];
+                    qowner = __float_as_uint(rays[DQ_META][e]);
                     qneed = true;
-                    const float d2 = V::dot(light_vec, light_vec);
-                    const float inv_len = rsqrt_native(d2);
-                    qo = V::axpy(P, N, 0.001f);                   // :394-399
-                    qd = V::scale(light_vec, inv_len);
-                    qt = d2 * inv_len - 0.001f;
-                    const float geometric = ((ss * inv_len) * -(sl * inv_len)) * rcp_native(d2);
+                }
+            }
+        } else {
+            // Small scenes: a scan is a few hundred instructions; the queued hits are resolved in place, one light
+            // per iteration (warp-uniform light index), the lanes whose sample is not needed idle through the scan.
+            const uint32_t cnt = tail - head;
+            if (sp_k < 0 && cnt > 0u) {
+                const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
+                const unsigned m_wait = __ballot_sync(0xffffffffu, mode == NM_WAIT);
+                if (cnt >= 32u || cnt + 2u * __popc(m_wait) >= 32u || !m_active) sp_k = 0;
+            }
+            spass = sp_k >= 0;
+            qn = cnt < 32u ? cnt : 32u;
+            qvalid = spass && lane < qn;
+            if (spass) {
+                unsigned lmask = 0;
+                if (qvalid) {
+                    const unsigned meta = __float_as_uint(ring[DQ_META][qe]);
+                    qowner = meta & 0xffu;
+                    lmask = meta >> 8;
+                    qrng = __float_as_uint(ring[DQ_RNG][qe]);
+                }
+                const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
+                int k = sp_k;
+                while (!((uni >> k) & 1u)) {                      // lights no queued hit can see: only their draws
+                    qrng = pcg_hash(pcg_hash(qrng));
+                    k++;
+                }
+                sp_k = k;
+                qrest = uni >> (k + 1);
+                const uint32_t s1 = pcg_hash(qrng);               // the two draws of :350-351 / :371-372, in order
+                qrng = pcg_hash(s1);
+                qt = -1.0f;                                       // nothing to find unless the sample is needed
+                if ((lmask >> k) & 1u) {
+                    const float3 P = f3(ring[DQ_PX][qe], ring[DQ_PY][qe], ring[DQ_PZ][qe]);
+                    const float3 N = f3(ring[DQ_NX][qe], ring[DQ_NY][qe], ring[DQ_NZ][qe]);
                     const float3 C = f3(ring[DQ_CX][qe], ring[DQ_CY][qe], ring[DQ_CZ][qe]);
-                    const float3 cc = V::mulv(V::scale(C, 0.31830988618f), V::scale(xyz(em), geometric * nl.w));
-                    qc = f3(fminf(cc.x, 10.0f), fminf(cc.y, 10.0f), fminf(cc.z, 10.0f));
+                    qneed = nee_sample(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
+                                       __uint2float_rn(qrng) * 2.3283064365386963e-10f, qo, qd, qt, qc);
                 }
             }
         }
@@ -243,17 +337,20 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
             else t_hit = tr.scan_native(qo, qd, qt, best);
         }
 
-        if (spass) {                                              // shader.wgsl:402-431 for the queued hits
+        if (spass) {                                              // shader.wgsl:402-431 for the queued samples
             if (qvalid) {
                 if (t_hit < 0.0f && qneed) {
                     atomicAdd(&s_late[0][qowner], qc.x);
                     atomicAdd(&s_late[1][qowner], qc.y);
                     atomicAdd(&s_late[2][qowner], qc.z);
                 }
-                if (qrest) ring[DQ_RNG][qe] = __uint_as_float(qrng);
+                if (SRC::kTiled) atomicAdd(&s_res[qowner], 1u);
+                else if (qrest) ring[DQ_RNG][qe] = __uint_as_float(qrng);
                 else atomicAdd(&s_res[qowner], 1u);
             }
-            if (qrest) {
+            if (SRC::kTiled) {
+                rhead += qn;
+            } else if (qrest) {
                 sp_k++;
             } else {
                 sp_k = -1;
@@ -317,7 +414,7 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
                 ring[DQ_CX][e] = mc.x * att.x; ring[DQ_CY][e] = mc.y * att.y; ring[DQ_CZ][e] = mc.z * att.z;
                 ring[DQ_RNG][e] = __uint_as_float(rng0);
                 ring[DQ_META][e] = __uint_as_float(tid | (lmask << 8));
-                pend++;
+                pend += SRC::kTiled ? (uint32_t)__popc(lmask) : 1u;      // units to resolve: light samples / the entry
             }
             tail += __popc(mp);
         }
