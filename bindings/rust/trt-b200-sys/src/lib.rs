@@ -120,6 +120,7 @@ extern "C" {
     pub fn trt_write_accumulation(ctx: *mut trt_ctx, src4: *const f32, n_pixels: usize) -> c_int;
     pub fn trt_get_counters(ctx: *mut trt_ctx, out: *mut trt_counters) -> c_int;
     pub fn trt_get_timings(ctx: *mut trt_ctx, out: *mut trt_timings) -> c_int;
+    pub fn trt_trace_kernel_name(ctx: *const trt_ctx) -> *const c_char;
     pub fn trt_get_frame_stats(ctx: *mut trt_ctx, out: *mut trt_frame_stats) -> c_int;
     pub fn trt_measure_fp32_peak(device: c_int, tflops: *mut f32, sm_count: *mut c_int, clock_khz: *mut c_int) -> c_int;
     pub fn trt_selftest_div3(device: c_int, n_cases: u64, seed: u32, distribution: c_int, mismatches: *mut u64, first_bad4: *mut f32) -> c_int;

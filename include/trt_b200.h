@@ -171,6 +171,9 @@ int trt_read_variance(trt_ctx *ctx, trt_variance *dst, size_t n_pixels);
 int trt_write_accumulation(trt_ctx *ctx, const float *src4, size_t n_pixels);
 int trt_get_counters(trt_ctx *ctx, trt_counters *out);
 int trt_get_timings(trt_ctx *ctx, trt_timings *out);
+/* name of the trace kernel the last frame ran (static builds, or a scene-specialised kernel compiled at upload time
+ * by NVRTC -- the counterpart of the reference's create_shader_module + create_compute_pipeline, lib.rs:321-352) */
+const char *trt_trace_kernel_name(const trt_ctx *ctx);
 int trt_get_frame_stats(trt_ctx *ctx, trt_frame_stats *out);
 /* register-resident FFMA loop on every SM: the measured FP32 FMA peak of this GPU in TFLOP/s
  * (roofline denominator cross-check; nominal = SMs x 128 lanes x 2 x clock) */

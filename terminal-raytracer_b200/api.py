@@ -115,6 +115,7 @@ SYMBOLS = {
     "trt_read_variance": (C.c_int, [_P, _P, C.c_size_t]),
     "trt_write_accumulation": (C.c_int, [_P, _P, C.c_size_t]),
     "trt_get_counters": (C.c_int, [_P, C.POINTER(Counters)]),
+    "trt_trace_kernel_name": (C.c_char_p, [_P]),
     "trt_get_timings": (C.c_int, [_P, C.POINTER(Timings)]),
     "trt_get_frame_stats": (C.c_int, [_P, C.POINTER(FrameStats)]),
     "trt_measure_fp32_peak": (C.c_int, [C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
@@ -337,6 +338,10 @@ class Renderer:
         n = C.c_size_t()
         self._ck(lib().trt_render_frame(self.h, C.byref(u), mode, host_ptr, cap, C.byref(n)))
         return n.value
+
+    def kernel_name(self) -> str:
+        """name of the trace kernel the last frame ran"""
+        return (lib().trt_trace_kernel_name(self.h) or b"").decode()
 
     def trace_async(self, u: Uniforms):
         self.size = (u.width, u.height)

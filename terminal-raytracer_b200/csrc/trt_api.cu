@@ -21,7 +21,7 @@ cudaError_t native_blend_launch(float4 *cur, const uint2 *batch, uint32_t n_batc
                                 uint32_t width, float4 *accumulation, float4 *pixels, cudaStream_t stream);
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
-                                cudaStream_t stream, uint32_t *launches);
+                                cudaStream_t stream, uint32_t *launches, const char **kernel_name);
 }
 
 struct trt_ctx {
@@ -81,6 +81,8 @@ struct trt_ctx {
     size_t batch_stream_cap = 0;
     uint64_t *h_batch_len = nullptr;   // pinned, one length per frame of the chunk
     size_t batch_len_cap = 0;
+
+    const char *kernel_name = "";      // trace kernel of the last frame (trt_trace_kernel_name)
 
     trt_uniforms last_u{};
     bool have_frame = false;
@@ -269,6 +271,9 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
                 sm.tri_e2[j] = make_float4(p.triangle_v2.x - p.triangle_v0.x, p.triangle_v2.y - p.triangle_v0.y, p.triangle_v2.z - p.triangle_v0.z, 0.0f);
             }
         }
+        sm.n_lights = (int)light_prim.size();
+        for (size_t k = 0; k < light_prim.size() && k < 32; k++)
+            if (prims[light_prim[k]].primitive_type == 0u) { sm.light_spheres |= 1 << k; sm.n_light_spheres++; }
         ctx->small = sm;
     }
     // tiles of the CTA-cooperative scan: at most TRT_TILE consecutive primitives of one run, in scan order
@@ -460,10 +465,11 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
             // the work counters are those of the as-written shader: conv 2 contexts count with conv 0 arithmetic
             if (ctx->cfg.conv == 1u) trace_pixel_kernel<1, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
             else trace_pixel_kernel<0, true><<<blocks, 128, 0, ctx->stream>>>(ctx->sv, ctx->lv, fp);
+            ctx->kernel_name = "trace_pixel_kernel<CONV, count>";
             ctx->launches += 1;
         } else if (ctx->cfg.conv == 2u) {
             cudaError_t e = native_trace_launch(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, &ctx->small, fp, ctx->sm_count,
-                                                ctx->stream, &ctx->launches);
+                                                ctx->stream, &ctx->launches, &ctx->kernel_name);
             if (e != cudaSuccess) { ctx->err = std::string("native trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
         } else {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
@@ -475,6 +481,8 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
                                            ctx->stream, &ctx->launches);
             }
             if (e != cudaSuccess) { ctx->err = std::string("trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
+            ctx->kernel_name = use_v1 && !n_batch ? "trace_persistent_kernel" : scene_fits_constant(ctx->sv) ? "trace_wave_kernel<CONV, SrcConst>"
+                                                                                                          : "trace_wave_kernel<CONV, SrcGlobal>";
         }
         CK(cudaGetLastError());
     }
@@ -731,6 +739,8 @@ extern "C" int trt_render_frames(trt_ctx *ctx, const trt_uniforms *u, uint32_t n
     if (frame_len) { for (uint32_t i = 0; i + 1 < n; i++) frame_len[i] = 0; frame_len[n - 1] = nlast; }
     return rc;
 }
+
+extern "C" const char *trt_trace_kernel_name(const trt_ctx *ctx) { return ctx ? ctx->kernel_name : ""; }
 
 extern "C" int trt_get_timings(trt_ctx *ctx, trt_timings *out) {
     if (!ctx || !out) return TRT_ERR_INVALID;

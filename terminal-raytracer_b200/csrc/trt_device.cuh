@@ -5,9 +5,20 @@
 // its own, so TRT_CONV_AS_WRITTEN is one IEEE rounding per WGSL operator, and TRT_CONV_FUSED fuses
 // exactly where __fmaf_rn is written below (DESIGN.md "Arithmetic conventions").
 #pragma once
+#ifdef __CUDACC_RTC__
+// run-time compilation (trt_jit.cpp): NVRTC has the CUDA built-ins but no host headers
+typedef unsigned char uint8_t;
+typedef int int32_t;
+typedef unsigned int uint32_t;
+typedef unsigned long long uint64_t;
+struct trt_variance { float variance; uint32_t sample_count; };     // include/trt_b200.h
+#define TRT_CONSTANT(decl) extern "C" { __constant__ decl; }        // findable by name in the loaded module
+#else
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/trt_b200.h"
+#define TRT_CONSTANT(decl) static __constant__ decl
+#endif
 
 namespace trt {
 

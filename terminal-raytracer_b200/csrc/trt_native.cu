@@ -14,6 +14,7 @@
 #include "trt_persistent.cuh"
 #include "trt_wave.cuh"
 #include "trt_native.cuh"
+#include "trt_jit.cuh"
 #include <cstdlib>
 #include <cstring>
 
@@ -21,7 +22,7 @@ namespace trt {
 
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
-                                cudaStream_t stream, uint32_t *launches) {
+                                cudaStream_t stream, uint32_t *launches, const char **kernel_name) {
     // this translation unit has its own __constant__ mirrors of the scene; rebinding synchronises the device
     static ConstOwner small_owner[64];
     const bool rebind = device >= 0 && device < 64 && !(small_owner[device].key == ctx_key && small_owner[device].serial == serial);
@@ -65,15 +66,42 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         memcpy(&kind, &small->pl_p[j].w, 4);
         cornell = kind == ShapeCornell::kind(j);
     }
-    if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
-        if (cornell) trace_native_kernel<SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
-        else if (constant) trace_native_kernel<SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
-        else if (sv.n_tiles > 0 && !force_untiled) {
+    cornell = cornell && sv.n_lights == ShapeCornell::NL && small->n_light_spheres == 0;
+    // a canonical small scene of any other shape gets a kernel compiled for that shape at run time (trt_jit.cuh)
+    JitKernel *jk = nullptr;
+    const int jit = jit_mode(nullptr);
+    if (!force_wave && !force_generic && constant && small->ok && sv.n_lights <= TRT_NV_MAX_LIGHTS && jit && (!cornell || jit == 2)) {
+        jk = jit_kernel_for(device, *small);
+        if (jk->ok) {
+            e = jit_bind_scene(*jk, ctx_key, serial, sv, lv, *small, stream);
+            if (e != cudaSuccess) return e;
+        } else {
+            jk = nullptr;
+        }
+    }
+    const char *name = "";
+    if (jk) {
+        void *args[] = {(void *)&sv, (void *)&lv, (void *)&fp};
+        e = cudaLaunchKernel((const void *)jk->kernel, dim3(blocks), dim3(TRT_NV_THREADS), args, 0, stream);
+        if (e != cudaSuccess) return e;
+        name = jk->name.c_str();
+    } else if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
+        if (cornell) {
+            trace_native_kernel<SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            name = "trace_native_kernel<SrcConst, ShapeCornell>";
+        } else if (constant) {
+            trace_native_kernel<SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            name = "trace_native_kernel<SrcConst, ShapeAny>";
+        } else if (sv.n_tiles > 0 && !force_untiled) {
             const uint32_t tcap = (uint32_t)sm_count * SrcTiled::kCtasPerSm;
             trace_native_kernel<SrcTiled, ShapeAny><<<want < tcap ? want : tcap, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            name = "trace_native_kernel<SrcTiled, ShapeAny>";
+        } else {
+            trace_native_kernel<SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            name = "trace_native_kernel<SrcGlobal, ShapeAny>";
         }
-        else trace_native_kernel<SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
     } else {
+        name = constant ? "trace_wave_kernel<2, SrcConst>" : "trace_wave_kernel<2, SrcGlobal>";
         const uint32_t wwant = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
         const uint32_t wcap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
         const uint32_t wblocks = wwant < wcap ? wwant : wcap;
@@ -81,6 +109,7 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         else trace_wave_kernel<2, SrcGlobal><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
     }
     *launches += 1;
+    if (kernel_name) *kernel_name = name;
     return cudaGetLastError();
 }
 

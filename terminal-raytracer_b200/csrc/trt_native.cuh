@@ -27,7 +27,7 @@
 // which a sample's light contributions are summed differs (rounding-level, inside conv 2's tolerance).
 // There is no limit on the number of lights beyond the 16-bit mask (TRT_NV_MAX_LIGHTS).
 #pragma once
-#include "trt_kernels.cuh"
+#include "trt_trace.cuh"
 
 namespace trt {
 
@@ -48,7 +48,7 @@ enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ
 // The sample of light k for a queued hit (shader.wgsl:350-429): sample point from the two draws (:352-389), the
 // two cosines (:403-404) and, when both are positive, the shadow ray (:394-399) and the clamped contribution
 // (:408-429).  Returns whether the shadow ray is needed.
-template <class TR>
+template <class SHAPE, class TR>
 __device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, float3 C, float r1, float r2, float3 &qo, float3 &qd,
                                            float &qt, float3 &qc) {
     typedef M<2> V;
@@ -57,7 +57,7 @@ __device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, fl
     const float4 em = tr.src.le(k);
     float3 light_vec;
     float sl;
-    if (__float_as_int(em.w) == 0) {                  // uniform sphere sampling :352-369
+    if (SHAPE::light_is_sphere(k, __float_as_int(em.w))) {   // uniform sphere sampling :352-369
         const float cos_theta = 1.0f - 2.0f * r1;
         const float sin_theta = sqrt_native(1.0f - cos_theta * cos_theta);
         float sp, cp;
@@ -86,9 +86,10 @@ __device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, fl
     return true;
 }
 
+// the kernel body; the __global__ entry points are trace_native_kernel below and, for a scene-specialised build
+// compiled at run time, trt_jit_trace (trt_jit.cpp)
 template <class SRC, class SHAPE>
-__global__ void __launch_bounds__(TRT_NV_THREADS, SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
-trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
+__device__ __forceinline__ void trace_native_body(const SceneView &sc, const LightView &lv, const FrameParams &fp) {
     typedef M<2> V;
     Counters<false> cn;
     Tracer<2, false, SRC> tr(sc, lv, fp, cn);
@@ -249,7 +250,7 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     const float3 P = f3(ring[DQ_PX][ee], ring[DQ_PY][ee], ring[DQ_PZ][ee]);
                     const float3 N = f3(ring[DQ_NX][ee], ring[DQ_NY][ee], ring[DQ_NZ][ee]);
                     const float3 C = f3(ring[DQ_CX][ee], ring[DQ_CY][ee], ring[DQ_CZ][ee]);
-                    needed = nee_sample(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
+                    needed = nee_sample<SHAPE>(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                         __uint2float_rn(erng) * 2.3283064365386963e-10f, so, sd, st, scn);
                     if (!needed) atomicAdd(&s_res[owner], 1u);
                 }
@@ -324,7 +325,7 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     const float3 P = f3(ring[DQ_PX][qe], ring[DQ_PY][qe], ring[DQ_PZ][qe]);
                     const float3 N = f3(ring[DQ_NX][qe], ring[DQ_NY][qe], ring[DQ_NZ][qe]);
                     const float3 C = f3(ring[DQ_CX][qe], ring[DQ_CY][qe], ring[DQ_CZ][qe]);
-                    qneed = nee_sample(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
+                    qneed = nee_sample<SHAPE>(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                        __uint2float_rn(qrng) * 2.3283064365386963e-10f, qo, qd, qt, qc);
                 }
             }
@@ -333,7 +334,9 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
         float t_hit = -1.0f;
         if (fp.max_depth != 0u) {
             if (small) t_hit = tr.template scan_small_native<SHAPE>(qo, qd, qt, best);
+#ifndef __CUDACC_RTC__
             else if (SRC::kTiled) t_hit = tr.scan_native_tiled(qo, qd, mode == NM_ACTIVE || spass ? qt : -1.0f, best, s_tile, spass);
+#endif
             else t_hit = tr.scan_native(qo, qd, qt, best);
         }
 
@@ -389,12 +392,14 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
         const uint32_t rng0 = rng;
         unsigned lmask = 0;
         const float hp_mag = 1.0f + fabsf(hp.x) + fabsf(hp.y) + fabsf(hp.z);
-        for (int k = 0; k < sc.n_lights; k++) {
+        const int n_lights = SHAPE::kFixedLights ? SHAPE::NL : sc.n_lights;
+#pragma unroll
+        for (int k = 0; k < n_lights; k++) {
             const uint32_t adv = pcg_hash(pcg_hash(rng));
             // a quantity that must be positive for the light to contribute, with a margin for the roundings of
             // the sample point and of the dot products (lb.w, lc.w: repack_kernel)
             float side;
-            if (__float_as_int(tr.src.le(k).w) == 0) {            // sphere: some of it above the tangent plane
+            if (SHAPE::light_is_sphere(k, __float_as_int(tr.src.le(k).w))) {   // sphere: some of it above the tangent plane
                 const float4 a = tr.src.la(k);
                 side = V::dot(hn, V::sub(xyz(a), hp)) + a.w;
             } else {                                              // triangle: the point in front of its plane
@@ -439,6 +444,12 @@ trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
         if (path_end) mode = NM_WAIT;
     }
     tr.flush_stats();
+}
+
+template <class SRC, class SHAPE>
+__global__ void __launch_bounds__(TRT_NV_THREADS, SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
+trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
+    trace_native_body<SRC, SHAPE>(sc, lv, fp);
 }
 
 }  // namespace trt

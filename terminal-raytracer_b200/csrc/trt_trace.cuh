@@ -2,7 +2,9 @@
 // device functions shared by the trace kernels.  Follows /root/reference/src/shader.wgsl (cited).
 #pragma once
 #include "trt_device.cuh"
+#ifndef __CUDACC_RTC__
 #include <cuda_pipeline.h>
+#endif
 
 namespace trt {
 
@@ -25,7 +27,7 @@ struct ConstScene {
     float4 la[TRT_CONST_LIGHTS], lb[TRT_CONST_LIGHTS], lc[TRT_CONST_LIGHTS], ln[TRT_CONST_LIGHTS], le[TRT_CONST_LIGHTS];
     int4 runs[TRT_CONST_RUNS];
 };
-static __constant__ ConstScene c_scene;      // one mirror per translation unit (strict / native builds)
+TRT_CONSTANT(ConstScene c_scene);      // one mirror per translation unit (strict / native builds)
 
 // Canonical small scene (conv 2 fast scan): the reference always pushes spheres, then planes, then
 // triangles (lib.rs:122-154), so a scene of at most TRT_SMALL_S/P/T of each is mirrored once more with
@@ -37,13 +39,14 @@ static __constant__ ConstScene c_scene;      // one mirror per translation unit 
 #define TRT_SMALL_T 4
 struct SmallScene {
     int ok, n_sph, n_pl, n_tri;
+    int n_lights, light_spheres, n_light_spheres, pad_;   // light list: count, bit k set = light k is a sphere
     float4 sph[TRT_SMALL_S];          // (c, r)
     float4 sph_r2[TRT_SMALL_S];       // (r*r, -, -, -)
     float4 pl_p[TRT_SMALL_P];         // (point, kind as int bits): kind 0 / 1 / 2 = normal is +-unit x / y / z, 3 = general
     float4 pl_n[TRT_SMALL_P];         // raw normal (general planes)
     float4 tri_v0[TRT_SMALL_T], tri_e1[TRT_SMALL_T], tri_e2[TRT_SMALL_T];
 };
-static __constant__ SmallScene c_small;
+TRT_CONSTANT(SmallScene c_small);
 
 struct SrcGlobal {
     static constexpr bool kSmall = false;
@@ -85,19 +88,27 @@ struct SrcConst {
     __device__ __forceinline__ float4 le(int k) const { return c_scene.le[k]; }
 };
 
-// Compile-time description of a canonical small scene for scan_small_native: primitive counts and the
-// kind of every plane (2 bits each, first plane in the low bits; kinds as in SmallScene::pl_p.w).
-struct ShapeAny { static constexpr bool kFixed = false; static constexpr int NS = 0, NP = 0, NT = 0;
-                  static __device__ __forceinline__ constexpr int kind(int) { return 3; } };
-template <int NS_, int NP_, int NT_, unsigned KINDS_> struct ShapeFixed {
-    static constexpr bool kFixed = true;
-    static constexpr int NS = NS_, NP = NP_, NT = NT_;
-    static constexpr unsigned KINDS = KINDS_;
+// Compile-time description of a canonical small scene for scan_small_native: primitive counts, the kind of every
+// plane (2 bits each, first plane in the low bits; kinds as in SmallScene::pl_p.w) and, when NL >= 0, the number of
+// lights and which of them are spheres (bit k of LSPH; the others are triangles).
+struct ShapeAny {
+    static constexpr bool kFixed = false, kFixedLights = false;
+    static constexpr int NS = 0, NP = 0, NT = 0, NL = -1;
+    static __host__ __device__ __forceinline__ constexpr int kind(int) { return 3; }
+    static __host__ __device__ __forceinline__ constexpr bool light_is_sphere(int, int type) { return type == 0; }
+};
+template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSPH_ = 0u> struct ShapeFixed {
+    static constexpr bool kFixed = true, kFixedLights = NL_ >= 0;
+    static constexpr int NS = NS_, NP = NP_, NT = NT_, NL = NL_;
+    static constexpr unsigned KINDS = KINDS_, LSPH = LSPH_;
     static __host__ __device__ __forceinline__ constexpr int kind(int j) { return (int)((KINDS_ >> (2 * j)) & 3u); }
+    static __host__ __device__ __forceinline__ constexpr bool light_is_sphere(int k, int type) {
+        return NL_ < 0 ? type == 0 : LSPH_ == 0u ? false : LSPH_ == (1u << NL_) - 1u ? true : ((LSPH_ >> k) & 1u) != 0u;
+    }
 };
 // the reference's embedded default scene (lib.rs:107, src/scenes/Cornell_Box.json): 3 spheres, floor / ceiling
-// (y), right / left (x), front / back (z) walls, 2 triangles
-typedef ShapeFixed<3, 6, 2, 0xA05u> ShapeCornell;
+// (y), right / left (x), front / back (z) walls, 2 triangles, both of them lights
+typedef ShapeFixed<3, 6, 2, 0xA05u, 2, 0u> ShapeCornell;
 
 // Large scenes in the production kernel: the CTA scans together.  Each warp scanning 20 k primitives on its
 // own streams ~1 MB through a 256 KB L1 per scan (C4 measured: 0.65 % of FP32 peak, L2 -> L1 bound); here the
@@ -430,6 +441,7 @@ struct Tracer {
         return best >= 0 ? closest : -1.0f;
     }
 
+#ifndef __CUDACC_RTC__
     // CTA-cooperative form of scan_native (SrcTiled): every thread of the CTA must call it, the same number of
     // times.  `tile` = 2 x 3 x TRT_TILE float4 of shared memory.  any_hit: the caller only reads t < 0
     // (shader.wgsl:400-402), so a warp whose lanes have all found an occluder (or have nothing to look for)
@@ -468,6 +480,7 @@ struct Tracer {
         __syncthreads();                                      // the next scan restages buffer 0
         return best >= 0 ? closest : -1.0f;
     }
+#endif
 
     // conv 2, canonical small scene: the same tests in the same order, fully unrolled over fixed constant-bank
     // slots (a slot beyond the scene's count is skipped by a warp-uniform branch).  With a compile-time SHAPE

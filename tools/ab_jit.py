@@ -1,0 +1,20 @@
+"""A/B of the run-time specialised kernel: python tools/ab_jit.py [scene2|demo|cornell|cornell_swapped] (set TRT_B200_JIT=0 / force outside)"""
+import json, os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import __graft_entry__ as g
+pkg, O = g.load_package(), g.load_oracle()
+which = sys.argv[1] if len(sys.argv) > 1 else "scene2"
+S = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "scenes")
+sc = json.load(open(os.path.join(S, {"scene2": "scene2.json", "demo": "demo.json"}.get(which, "Cornell_Box.json"))))
+if which == "cornell_swapped":
+    sc["planes"] = sc["planes"][2:] + sc["planes"][:2]
+w, h, spp, depth = 1920, 1080, 64, 32
+prims = O.flatten_scene(sc)
+u = pkg.api.uniforms_from_bytes(O.make_uniforms(sc, len(prims), O.C1_SEED, 0, width=w, height=h, spp=spp, max_depth=depth).tobytes())
+r = pkg.Renderer(w, h, conv=2)
+t0 = time.perf_counter(); r.upload_scene(prims); r.render_frame(u, pkg.MODE_NONE); first = time.perf_counter() - t0
+best = 1e9
+for k in range(3):
+    r.render_frame(u, pkg.MODE_NONE); best = min(best, r.timings().trace_ms)
+st = r.frame_stats()
+print(f"{which}: {r.kernel_name()}: trace {best:.2f} ms, {st.samples_traced / best / 1e3:.1f} Msamples/s, {st.bounces / st.samples_traced:.2f} bounces/sample; first frame incl. upload/compile {first * 1e3:.0f} ms", flush=True)
