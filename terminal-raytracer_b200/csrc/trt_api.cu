@@ -250,7 +250,9 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
             else canon = false;
         }
         if (canon && ns <= TRT_SMALL_S && np <= TRT_SMALL_P && nt <= TRT_SMALL_T) {
-            sm.ok = 1; sm.n_sph = (int)ns; sm.n_pl = (int)np; sm.n_tri = (int)nt;
+            sm.jit_ok = 1;
+            sm.ok = ns <= TRT_STATIC_S && np <= TRT_STATIC_P && nt <= TRT_STATIC_T;
+            sm.n_sph = (int)ns; sm.n_pl = (int)np; sm.n_tri = (int)nt;
             for (uint32_t j = 0; j < ns; j++) {
                 const trt_primitive &p = prims[j];
                 sm.sph[j] = make_float4(p.sphere_center.x, p.sphere_center.y, p.sphere_center.z, p.sphere_radius);

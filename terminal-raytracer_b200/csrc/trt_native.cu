@@ -70,7 +70,7 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     // a canonical small scene of any other shape gets a kernel compiled for that shape at run time (trt_jit.cuh)
     JitKernel *jk = nullptr;
     const int jit = jit_mode(nullptr);
-    if (!force_wave && !force_generic && constant && small->ok && sv.n_lights <= TRT_NV_MAX_LIGHTS && jit && (!cornell || jit == 2)) {
+    if (!force_wave && !force_generic && constant && small->jit_ok && sv.n_lights <= TRT_NV_MAX_LIGHTS && jit && (!cornell || jit == 2)) {
         jk = jit_kernel_for(device, *small);
         if (jk->ok) {
             e = jit_bind_scene(*jk, ctx_key, serial, sv, lv, *small, stream);

@@ -34,12 +34,15 @@ TRT_CONSTANT(ConstScene c_scene);      // one mirror per translation unit (stric
 // one fixed constant-bank address per primitive: the unrolled scan reads its operands straight from
 // the constant bank (no address arithmetic, no loop control, no run dispatch).  Index of sphere j is
 // j, of plane j n_sph + j, of triangle j n_sph + n_pl + j.
-#define TRT_SMALL_S 4
+#define TRT_SMALL_S 24         // capacity of the mirror: what a run-time specialised kernel (trt_jit.cuh) can take
 #define TRT_SMALL_P 8
-#define TRT_SMALL_T 4
+#define TRT_SMALL_T 8
+#define TRT_STATIC_S 4         // slots the statically compiled run-time-count scan unrolls (ok: the scene fits these)
+#define TRT_STATIC_P 8
+#define TRT_STATIC_T 4
 struct SmallScene {
-    int ok, n_sph, n_pl, n_tri;
-    int n_lights, light_spheres, n_light_spheres, pad_;   // light list: count, bit k set = light k is a sphere
+    int ok, n_sph, n_pl, n_tri;       // ok: canonical order and within TRT_STATIC_*; jit_ok (below): within TRT_SMALL_*
+    int n_lights, light_spheres, n_light_spheres, jit_ok;   // light list: count, bit k set = light k is a sphere
     float4 sph[TRT_SMALL_S];          // (c, r)
     float4 sph_r2[TRT_SMALL_S];       // (r*r, -, -, -)
     float4 pl_p[TRT_SMALL_P];         // (point, kind as int bits): kind 0 / 1 / 2 = normal is +-unit x / y / z, 3 = general
@@ -495,7 +498,7 @@ struct Tracer {
         const int n_pl = SHAPE::kFixed ? SHAPE::NP : c_small.n_pl;
         const int n_tri = SHAPE::kFixed ? SHAPE::NT : c_small.n_tri;
 #pragma unroll
-        for (int j = 0; j < TRT_SMALL_S; j++) {
+        for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NS : TRT_STATIC_S); j++) {
             if (j < n_sph) {
                 uint32_t cost;
                 const float t = test_sphere(ro, rd, c_small.sph[j], c_small.sph_r2[j].x, t_min, closest, cost);
@@ -508,7 +511,7 @@ struct Tracer {
             const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
                                   fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
 #pragma unroll
-            for (int j = 0; j < TRT_SMALL_P; j++) {
+            for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NP : TRT_STATIC_P); j++) {
                 if (j < n_pl) {
                     const float4 p = c_small.pl_p[j];
                     const int kind = SHAPE::kFixed ? SHAPE::kind(j) : __float_as_int(p.w);
@@ -526,7 +529,7 @@ struct Tracer {
             }
         }
 #pragma unroll
-        for (int j = 0; j < TRT_SMALL_T; j++) {
+        for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NT : TRT_STATIC_T); j++) {
             if (j < n_tri) {
                 const float3 e1 = xyz(c_small.tri_e1[j]), e2 = xyz(c_small.tri_e2[j]);
                 const float3 h = V::cross(rd, e2);

@@ -8,10 +8,11 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import __graft_entry__ as g
 pkg, O = g.load_package(), g.load_oracle()
 frames = int(sys.argv[1]) if len(sys.argv) > 1 else 600
+conv = int(sys.argv[2]) if len(sys.argv) > 2 else 0       # 0: strict (frames checked bit for bit), 2: production arithmetic
 scene = pkg.Scene.parse(json.dumps(O.SCENE2))
 cam, ocam = pkg.Camera(), O.Camera()
 info = scene.info
-r = pkg.Renderer(info.width, info.height)
+r = pkg.Renderer(info.width, info.height, conv=conv)
 r.upload_scene(scene)
 oprims = O.flatten_scene(O.SCENE2)
 lat, checked, nbytes = [], 0, 0
@@ -29,14 +30,20 @@ for i in range(-20, frames):                       # 20 untimed warm-up frames
             ou = O.make_uniforms(O.SCENE2, len(oprims), O.c2_seed(i), 0, camera=ocam)
             assert bytes(u) == ou.tobytes()
             ref = O.render(oprims, ou)
-            assert np.array_equal(r.read_pixels().view(np.uint32), ref["pixels"].view(np.uint32))
-            assert stream == O.quantise(ref["pixels"], info.width, info.height, 0)[0]
+            if conv == 0:
+                assert np.array_equal(r.read_pixels().view(np.uint32), ref["pixels"].view(np.uint32))
+                assert stream == O.quantise(ref["pixels"], info.width, info.height, 0)[0]
+            else:                                   # conv 2: tolerance on the float frame, exact quantiser on its own pixels
+                got = r.read_pixels().reshape(-1, 4)[:, :3]; want = ref["pixels"].reshape(-1, 4)[:, :3]
+                rel = np.abs(got - want) / np.maximum(np.abs(want), 1e-2)
+                assert (rel.max(axis=1) > 1e-4).mean() < 0.02
+                assert stream == O.quantise(r.read_pixels(), info.width, info.height, 0)[0]
             checked += 1
     else:
         ocam.key(k)
 lat = np.array(lat)
 t = r.timings()
-print(json.dumps({"config": "C5 scene2.json 200x100 32spp depth4, 600 scripted keys, reset per move, ASCII",
+print(json.dumps({"config": "C5 scene2.json 200x100 32spp depth4, 600 scripted keys, reset per move, ASCII", "conv": conv, "kernel": r.kernel_name(),
                   "frames": frames, "p50_ms": float(np.percentile(lat, 50)), "p99_ms": float(np.percentile(lat, 99)),
                   "mean_ms": float(lat.mean()), "max_ms": float(lat.max()), "fps": 1e3 / float(lat.mean()),
                   "bytes_per_frame": nbytes // frames, "last_frame_device_ms": {"trace": t.trace_ms, "quantise": t.quantise_ms, "d2h": t.d2h_ms},
