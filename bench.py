@@ -319,7 +319,7 @@ def ours(args):
             traffic = ent["dram_bytes_per_launch"]
     except (OSError, ValueError, KeyError):
         pass
-    roofline = {"bound": "fp32", "kernel": "trace_native_kernel" if args.conv == 2 else "trace_wave_kernel",
+    roofline = {"bound": "fp32", "kernel": sr.r.kernel_name(),
                 "achieved": achieved, "peak": NOMINAL_FP32_TFLOPS,
                 "unit": "TFLOP/s", "frac": achieved / NOMINAL_FP32_TFLOPS, "traffic": traffic,
                 "traffic_unit": "bytes of DRAM read + written per launch (ncu --set full, profiles/traffic.json)",
