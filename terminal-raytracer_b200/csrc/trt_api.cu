@@ -273,6 +273,11 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
                 sm.tri_e2[j] = make_float4(p.triangle_v2.x - p.triangle_v0.x, p.triangle_v2.y - p.triangle_v0.y, p.triangle_v2.z - p.triangle_v0.z, 0.0f);
             }
         }
+        for (int j = 0; j < sm.n_tri && j < 5 && sm.jit_ok; j++) {
+            const float e[6] = {sm.tri_e1[j].x, sm.tri_e1[j].y, sm.tri_e1[j].z, sm.tri_e2[j].x, sm.tri_e2[j].y, sm.tri_e2[j].z};
+            for (int b = 0; b < 6; b++)
+                if (e[b] == 0.0f) sm.tri_zero |= 1u << (6 * j + b);
+        }
         sm.n_lights = (int)light_prim.size();
         for (size_t k = 0; k < light_prim.size() && k < 32; k++)
             if (prims[light_prim[k]].primitive_type == 0u) { sm.light_spheres |= 1 << k; sm.n_light_spheres++; }

@@ -66,7 +66,7 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         memcpy(&kind, &small->pl_p[j].w, 4);
         cornell = kind == ShapeCornell::kind(j);
     }
-    cornell = cornell && sv.n_lights == ShapeCornell::NL && small->n_light_spheres == 0;
+    cornell = cornell && sv.n_lights == ShapeCornell::NL && small->n_light_spheres == 0 && small->tri_zero == ShapeCornell::TZ;
     // a canonical small scene of any other shape gets a kernel compiled for that shape at run time (trt_jit.cuh)
     JitKernel *jk = nullptr;
     const int jit = jit_mode(nullptr);

@@ -42,7 +42,8 @@ TRT_CONSTANT(ConstScene c_scene);      // one mirror per translation unit (stric
 #define TRT_STATIC_T 4
 struct SmallScene {
     int ok, n_sph, n_pl, n_tri;       // ok: canonical order and within TRT_STATIC_*; jit_ok (below): within TRT_SMALL_*
-    int n_lights, light_spheres, n_light_spheres, jit_ok;   // light list: count, bit k set = light k is a sphere
+    int n_lights, light_spheres, n_light_spheres, jit_ok;
+    unsigned tri_zero, pad0_, pad1_, pad2_;               // ShapeFixed::TZ of this scene   // light list: count, bit k set = light k is a sphere
     float4 sph[TRT_SMALL_S];          // (c, r)
     float4 sph_r2[TRT_SMALL_S];       // (r*r, -, -, -)
     float4 pl_p[TRT_SMALL_P];         // (point, kind as int bits): kind 0 / 1 / 2 = normal is +-unit x / y / z, 3 = general
@@ -99,8 +100,9 @@ struct ShapeAny {
     static constexpr int NS = 0, NP = 0, NT = 0, NL = -1;
     static __host__ __device__ __forceinline__ constexpr int kind(int) { return 3; }
     static __host__ __device__ __forceinline__ constexpr bool light_is_sphere(int, int type) { return type == 0; }
+    static __host__ __device__ __forceinline__ constexpr unsigned tri_zero(int) { return 0u; }
 };
-template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSPH_ = 0u> struct ShapeFixed {
+template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSPH_ = 0u, unsigned TZ_ = 0u> struct ShapeFixed {
     static constexpr bool kFixed = true, kFixedLights = NL_ >= 0;
     static constexpr int NS = NS_, NP = NP_, NT = NT_, NL = NL_;
     static constexpr unsigned KINDS = KINDS_, LSPH = LSPH_;
@@ -108,10 +110,13 @@ template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSP
     static __host__ __device__ __forceinline__ constexpr bool light_is_sphere(int k, int type) {
         return NL_ < 0 ? type == 0 : LSPH_ == 0u ? false : LSPH_ == (1u << NL_) - 1u ? true : ((LSPH_ >> k) & 1u) != 0u;
     }
+    // 6 bits per triangle (the first five): e1.x e1.y e1.z e2.x e2.y e2.z are exactly zero (axis-aligned edges)
+    static constexpr unsigned TZ = TZ_;
+    static __host__ __device__ __forceinline__ constexpr unsigned tri_zero(int j) { return j < 5 ? (TZ_ >> (6 * j)) & 63u : 0u; }
 };
 // the reference's embedded default scene (lib.rs:107, src/scenes/Cornell_Box.json): 3 spheres, floor / ceiling
 // (y), right / left (x), front / back (z) walls, 2 triangles, both of them lights
-typedef ShapeFixed<3, 6, 2, 0xA05u, 2, 0u> ShapeCornell;
+typedef ShapeFixed<3, 6, 2, 0xA05u, 2, 0u, 0x4DEu> ShapeCornell;      // light quad: edges along x and z
 
 // Large scenes in the production kernel: the CTA scans together.  Each warp scanning 20 k primitives on its
 // own streams ~1 MB through a 256 KB L1 per scan (C4 measured: 0.65 % of FP32 peak, L2 -> L1 bound); here the
@@ -133,6 +138,25 @@ struct TileAcc {
     __device__ __forceinline__ float4 gc(int i) const { return c[i - base]; }
     __device__ __forceinline__ float ga_axis(int i, int axis) const { return reinterpret_cast<const float *>(&a[i - base])[axis]; }
 };
+
+// Products with a constant that is exactly zero, dropped at compile time (run-time specialised scan: the flags are
+// template constants once the loop is unrolled).  Exact for finite operands: x * 0 = 0, y - 0 = y, and a chain of
+// fused multiply-adds that starts at 0 equals the chain without that term.  a * b - c * d, constants b and d:
+__device__ __forceinline__ float dpz(float a, float b, bool zb, float c, float d, bool zd) {
+    if (zb && zd) return 0.0f;
+    if (zd) return a * b;
+    if (zb) return -(c * d);
+    return __fmaf_rn(a, b, -(c * d));
+}
+// dot(a, b) = fma(a.z, b.z, fma(a.y, b.y, a.x * b.x)) over the terms that are not known to be zero
+__device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool z2) {
+    float r = 0.0f;
+    bool have = false;
+    if (!z0) { r = a.x * b.x; have = true; }
+    if (!z1) { r = have ? __fmaf_rn(a.y, b.y, r) : a.y * b.y; have = true; }
+    if (!z2) { r = have ? __fmaf_rn(a.z, b.z, r) : a.z * b.z; }
+    return r;
+}
 
 template <int CONV, bool COUNT, class SRC>
 struct Tracer {
@@ -531,18 +555,25 @@ struct Tracer {
 #pragma unroll
         for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NT : TRT_STATIC_T); j++) {
             if (j < n_tri) {
+                // hit_triangle (shader.wgsl:192-223); z = which edge components are exactly zero (ShapeFixed::TZ)
+                const unsigned z = SHAPE::tri_zero(j);
+                const bool e1x0 = z & 1u, e1y0 = z & 2u, e1z0 = z & 4u, e2x0 = z & 8u, e2y0 = z & 16u, e2z0 = z & 32u;
                 const float3 e1 = xyz(c_small.tri_e1[j]), e2 = xyz(c_small.tri_e2[j]);
-                const float3 h = V::cross(rd, e2);
-                const float a = V::dot(e1, h);
+                const float3 h = f3(dpz(rd.y, e2.z, e2z0, rd.z, e2.y, e2y0), dpz(rd.z, e2.x, e2x0, rd.x, e2.z, e2z0),
+                                    dpz(rd.x, e2.y, e2y0, rd.y, e2.x, e2x0));                       // cross(rd, e2)
+                const bool hx0 = e2z0 && e2y0, hy0 = e2x0 && e2z0, hz0 = e2y0 && e2x0;
+                const float a = dotz(e1, h, e1x0 || hx0, e1y0 || hy0, e1z0 || hz0);
                 if (!(a > -0.00001f && a < 0.00001f)) {
                     const float f = rcp_native(a);
                     const float3 s = V::sub(ro, xyz(c_small.tri_v0[j]));
-                    const float u = f * V::dot(s, h);
+                    const float u = f * dotz(s, h, hx0, hy0, hz0);
                     if (!(u < 0.0f || u > 1.0f)) {
-                        const float3 q = V::cross(s, e1);
-                        const float v = f * V::dot(rd, q);
+                        const float3 q = f3(dpz(s.y, e1.z, e1z0, s.z, e1.y, e1y0), dpz(s.z, e1.x, e1x0, s.x, e1.z, e1z0),
+                                            dpz(s.x, e1.y, e1y0, s.y, e1.x, e1x0));                   // cross(s, e1)
+                        const bool qx0 = e1z0 && e1y0, qy0 = e1x0 && e1z0, qz0 = e1y0 && e1x0;
+                        const float v = f * dotz(rd, q, qx0, qy0, qz0);
                         if (!(v < 0.0f || u + v > 1.0f)) {
-                            const float t = f * V::dot(e2, q);
+                            const float t = f * dotz(e2, q, e2x0 || qx0, e2y0 || qy0, e2z0 || qz0);
                             if (t > t_min && t < closest) { closest = t; best = n_sph + n_pl + j; }
                         }
                     }
