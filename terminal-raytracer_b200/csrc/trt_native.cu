@@ -105,8 +105,13 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         const uint32_t wwant = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
         const uint32_t wcap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
         const uint32_t wblocks = wwant < wcap ? wwant : wcap;
-        if (constant) trace_wave_kernel<2, SrcConst><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
-        else trace_wave_kernel<2, SrcGlobal><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        if (constant) {
+            if (fp.batch) trace_wave_kernel<2, SrcConst, true><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+            else trace_wave_kernel<2, SrcConst, false><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        } else {
+            if (fp.batch) trace_wave_kernel<2, SrcGlobal, true><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+            else trace_wave_kernel<2, SrcGlobal, false><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        }
     }
     *launches += 1;
     if (kernel_name) *kernel_name = name;

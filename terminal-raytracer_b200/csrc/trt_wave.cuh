@@ -33,7 +33,9 @@ namespace trt {
 
 enum { WM_CLOSEST = 0, WM_SHADOW = 1, WM_NEED_PIXEL = 2, WM_DONE = 3 };
 
-template <int CONV, class SRC>
+// BATCH: the frame-batch form (work item = (frame, pixel), trt_render_frames); the single-frame instantiation carries
+// neither the extra state nor the branches
+template <int CONV, class SRC, bool BATCH>
 __global__ void __launch_bounds__(TRT_WV_THREADS, TRT_WV_CTAS_PER_SM)
 trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
     typedef M<CONV> V;
@@ -44,7 +46,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
 
     int mode = WM_NEED_PIXEL;
     uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0, fslot = 0;
-    const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
+    const uint32_t n_work = BATCH ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     bool extra_phase = false;
     float variance_value = 0.0f;
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
@@ -69,7 +71,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                 const uint32_t slot = base + __popc(need & lt_mask);
                 if (slot < n_work) {
                     uint32_t ls = slot, seed = fp.seed, frame_number = fp.frame_number;
-                    if (fp.batch) {                              // frame batch: work item = (frame, local pixel)
+                    if (BATCH) {                                 // frame batch: work item = (frame, local pixel)
                         const uint32_t f = slot / fp.n_local_pixels;
                         ls = slot - f * fp.n_local_pixels;
                         const uint2 b = __ldg(&fp.batch[f]);
@@ -80,7 +82,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
                     const uint32_t x = lp - lr * fp.width;
                     const uint32_t y = fp.row_map ? fp.row_map[lr] : lr;
                     xy = x | (y << 16);
-                    fslot = slot - ls + lp;
+                    if (BATCH) fslot = slot - ls + lp;
                     rng = (y * fp.width + x) * 1973u + seed * 9277u + frame_number * 12345u;   // shader.wgsl:507
                     pixel_color = f3(0, 0, 0);
                     sq_sum = f3(0, 0, 0);
@@ -253,7 +255,7 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
             }
             if (finished) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
-                tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, fslot);
+                tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, BATCH ? fslot : 0u);
                 mode = WM_NEED_PIXEL;
             } else {                                              // next sample (shader.wgsl:517 / :565)
                 rng = pcg_hash(rng + si * 5096u);
@@ -278,13 +280,19 @@ static inline cudaError_t wave_trace_launch(const SceneView &sv, const LightView
     const uint32_t want = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
     const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
     const uint32_t blocks = want < cap ? want : cap;
+#define TRT_WV_LAUNCH(CONV_, SRC_)                                                                                  \
+    do {                                                                                                            \
+        if (fp.batch) trace_wave_kernel<CONV_, SRC_, true><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);      \
+        else trace_wave_kernel<CONV_, SRC_, false><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);              \
+    } while (0)
     if (small) {
-        if (conv) trace_wave_kernel<1, SrcConst><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
-        else trace_wave_kernel<0, SrcConst><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        if (conv) TRT_WV_LAUNCH(1, SrcConst);
+        else TRT_WV_LAUNCH(0, SrcConst);
     } else {
-        if (conv) trace_wave_kernel<1, SrcGlobal><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
-        else trace_wave_kernel<0, SrcGlobal><<<blocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        if (conv) TRT_WV_LAUNCH(1, SrcGlobal);
+        else TRT_WV_LAUNCH(0, SrcGlobal);
     }
+#undef TRT_WV_LAUNCH
     *launches += 1;
     return cudaGetLastError();
 }
