@@ -84,6 +84,12 @@ struct trt_ctx {
 
     const char *kernel_name = "";      // trace kernel of the last frame (trt_trace_kernel_name)
 
+    // work of the last single frame (samples, bounces: d_stats[0..1]) copied to h_len[4..5] behind the trace kernel;
+    // read without waiting at the next launch to choose the number of resident CTAs (frame_ctas_hint)
+    cudaEvent_t ev_stats = nullptr;
+    bool stats_valid = false;
+    uint32_t stats_w = 0, stats_h = 0, stats_pixels = 0, stats_spp = 0, stats_depth = 0;
+
     trt_uniforms last_u{};
     bool have_frame = false;
     trt_timings tm{};
@@ -121,6 +127,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
     if (ctx->h_batch_len) cudaFreeHost(ctx->h_batch_len);
     for (auto &e : ctx->ev) if (e) cudaEventDestroy(e);
+    if (ctx->ev_stats) cudaEventDestroy(ctx->ev_stats);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -164,8 +171,8 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         CK(cudaMalloc(&ctx->d_counters, K_COUNT * sizeof(unsigned long long)));
         CK(cudaMemsetAsync(ctx->d_counters, 0, K_COUNT * sizeof(unsigned long long), ctx->stream));
         CK(cudaMalloc(&ctx->d_work, 64 + 2 * TRT_ORDER_BUCKETS * sizeof(unsigned int)));
-        CK(cudaMalloc(&ctx->d_stats, 64));
-        CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
+        CK(cudaMalloc(&ctx->d_stats, TRT_STATS_BYTES));
+        CK(cudaMemsetAsync(ctx->d_stats, 0, TRT_STATS_BYTES, ctx->stream));
         CK(cudaMalloc(&ctx->d_order, ctx->max_pixels * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_map, (size_t)cfg->max_height * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_src, (size_t)cfg->max_height * sizeof(uint64_t)));
@@ -418,6 +425,24 @@ static int check_uniforms(trt_ctx *ctx, const trt_uniforms *u) {
 
 // One launch of the trace kernel for the frame `u` describes; with n_batch > 0 for the n_batch frames whose
 // (seed, frame_number) pairs are in ctx->d_batch (means into ctx->d_batch_cur, blended by the caller).
+// Resident CTAs per SM for this frame.  A pixel is one serial chain (its random-number state runs through all its
+// samples, shader.wgsl:517/:565): no frame can be shorter than its longest pixel, and a chain advances at the SM's
+// issue rate divided by the resident warps.  When the frame is long against the longest possible chain (spp x
+// max_depth bounces) every CTA that fits is worth its throughput (C3 on one GPU: 8 CTAs 760 ms, 7: 769 ms); when a
+// shard of the frame gets short, fewer resident warps make the critical chains faster for a smaller loss (a quarter
+// of C3: 8 CTAs 219 ms, 7: 199 ms; an eighth: 108 / 101 ms; a sixteenth: 61 / 59 / 55 ms with 6).  R = longest
+// possible chain / bounces per resident lane, from the previous frame's bounce count; no history: all that fit.
+static uint32_t frame_ctas_hint(trt_ctx *ctx, const FrameParams &fp) {
+    if (!ctx->stats_valid || ctx->stats_w != fp.width || ctx->stats_h != fp.height || ctx->stats_pixels != fp.n_local_pixels ||
+        ctx->stats_spp != fp.spp || ctx->stats_depth != fp.max_depth) return 0u;
+    if (cudaEventQuery(ctx->ev_stats) != cudaSuccess) { cudaGetLastError(); return 0u; }
+    const double bounces = (double)ctx->h_len[5];
+    if (!(bounces > 0.0)) return 0u;
+    const double lanes = (double)ctx->sm_count * 8.0 * 128.0;
+    const double r = (double)fp.spp * (double)(fp.max_depth ? fp.max_depth : 1u) * lanes / bounces;
+    return r < 0.5 ? 0u : r < 2.5 ? 7u : 6u;
+}
+
 static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     int rc = check_uniforms(ctx, u);
     if (rc) return rc;
@@ -449,7 +474,7 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
         if (ctx->cfg.count_work) return fail(ctx, TRT_ERR_INVALID, "frame batch on an instrumented (count_work) context");
         fp.batch = ctx->d_batch; fp.batch_cur = ctx->d_batch_cur; fp.n_batch = n_batch;
     } else {
-        CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
+        CK(cudaMemsetAsync(ctx->d_stats, 0, TRT_STATS_BYTES, ctx->stream));
         ctx->launches = 0;
         CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     }
@@ -466,6 +491,7 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
         ctx->launches += 1;
         fp.order = ctx->d_order;
     }
+    if (!n_batch) fp.ctas_hint = frame_ctas_hint(ctx, fp);
     if (fp.n_local_pixels) {
         if (ctx->cfg.count_work) {
             const uint32_t blocks = (fp.n_local_pixels + 127u) / 128u;
@@ -493,7 +519,15 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
         }
         CK(cudaGetLastError());
     }
-    if (!n_batch) CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    if (!n_batch) {
+        CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+        if (!ctx->ev_stats) CK(cudaEventCreateWithFlags(&ctx->ev_stats, cudaEventDisableTiming));
+        CK(cudaMemcpyAsync(ctx->h_len + 4, ctx->d_stats, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaEventRecord(ctx->ev_stats, ctx->stream));
+        ctx->stats_valid = true;
+        ctx->stats_w = u->width; ctx->stats_h = u->height; ctx->stats_pixels = fp.n_local_pixels;
+        ctx->stats_spp = fp.spp; ctx->stats_depth = fp.max_depth;
+    }
     ctx->last_u = *u;
     ctx->have_frame = true;
     ctx->order_w = u->width;
@@ -684,7 +718,7 @@ extern "C" int trt_render_frames(trt_ctx *ctx, const trt_uniforms *u, uint32_t n
             ctx->batch_len_cap = chunk;
         }
     }
-    CK(cudaMemsetAsync(ctx->d_stats, 0, 64, ctx->stream));
+    CK(cudaMemsetAsync(ctx->d_stats, 0, TRT_STATS_BYTES, ctx->stream));
     ctx->launches = 0;
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     size_t off = 0;
@@ -826,6 +860,7 @@ extern "C" int trt_device_buffer(trt_ctx *ctx, int which, void **dptr, size_t *b
         case 1: *dptr = ctx->d_accum; n = ctx->max_pixels * sizeof(float4); break;
         case 2: *dptr = ctx->d_variance; n = ctx->max_pixels * sizeof(trt_variance); break;
         case 3: *dptr = ctx->d_stream; n = ctx->stream_cap; break;
+        case 4: *dptr = ctx->d_stats; n = TRT_STATS_BYTES; break;      // frame statistics + the diagnostic words of a measurement build
         default: return fail(ctx, TRT_ERR_INVALID, "device_buffer: unknown buffer id");
     }
     if (bytes) *bytes = n;

@@ -45,6 +45,7 @@ struct SceneView {
 
 #define TRT_CONST_PRIMS 256     // scenes up to this size are also mirrored in __constant__ memory
 
+#define TRT_STATS_BYTES (8 * (8 + 2 * 512))     // 8 words of frame statistics + two 512-bin histograms (measurement builds)
 struct FrameParams {
     uint32_t width, height, spp, max_depth;
     uint32_t seed, frame_number, base_samples, n_local_pixels;
@@ -58,13 +59,14 @@ struct FrameParams {
     trt_variance *variance;
     unsigned long long *counters;   // trt_counters as 19 x u64 (instrumented build only)
     unsigned int *work_counter;     // persistent kernel: next pixel to hand out
-    unsigned long long *stats;      // [0] samples traced, [1] closest-hit scans (bounces) of this frame
+    unsigned long long *stats;      // [0] samples traced, [1] closest-hit scans (bounces) of this frame; [2..]: diagnostics
     // frame batch (trt_render_frames): n_batch frames that differ only in (seed, frame_number) are traced by one
     // launch; work item = (frame, local pixel); a finished pixel stores its mean into batch_cur[frame][local pixel]
     // and blend_frames_kernel applies the temporal blend (shader.wgsl:610-619) in frame order afterwards
     const uint2 *batch;             // (seed, frame_number) per frame; NULL: single frame
     float4 *batch_cur;
     uint32_t n_batch;
+    uint32_t ctas_hint;             // host only: resident CTAs per SM the launcher should use (0: all that fit)
 };
 
 // shader.wgsl:610-619: the temporal blend of one pixel, with explicit roundings so that every call site

@@ -55,7 +55,11 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     }
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     const uint32_t want = (n_work + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
-    const uint32_t cap = (uint32_t)sm_count * TRT_NV_CTAS_PER_SM;
+    // resident CTAs per SM: the caller's hint (trt_api.cu frame_ctas_hint), else all that fit (8); TRT_B200_CTAS overrides (A/B)
+    static const char *ctas_env = getenv("TRT_B200_CTAS");
+    uint32_t ctas = fp.ctas_hint >= 1u && fp.ctas_hint < TRT_NV_CTAS_PER_SM ? fp.ctas_hint : TRT_NV_CTAS_PER_SM;
+    if (ctas_env && atoi(ctas_env) >= 1 && atoi(ctas_env) <= TRT_NV_CTAS_PER_SM) ctas = (uint32_t)atoi(ctas_env);
+    const uint32_t cap = (uint32_t)sm_count * ctas;
     const uint32_t blocks = want < cap ? want : cap;
     // the reference's default scene shape (3 spheres, 6 axis-aligned walls in y y x x z z order, 2 triangles)
     // has a compile-time specialised scan; any other scene takes the same kernel with run-time counts

@@ -124,6 +124,19 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     float3 ro = f3(0, 0, 0), rd = f3(0, 0, 1);   // this lane's closest-hit ray
     const bool small = SHAPE::kFixed || (SRC::kSmall && c_small.ok);
 
+#if TRT_TAIL_DIAG
+    // measurement build: when (0.5 ms bins from the first warp's start) this warp first found the work list empty
+    // -> stats[520 + bin], and when it left -> stats[8 + bin]
+    unsigned long long t_base;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_base));
+    {
+        const unsigned long long old = atomicCAS(&fp.stats[2], 0ull, t_base);
+        if (old) t_base = old;
+        t_base = __shfl_sync(0xffffffffu, t_base, 0);
+    }
+    bool saw_dry = false;
+    unsigned long long t_pix = 0;
+#endif
     for (;;) {
         // ---- finish the sample of a lane whose path has ended and whose queue entries are all resolved ------
         // (shader.wgsl:548-551, :555-565, :596-621)
@@ -154,6 +167,15 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             if (finished) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
                 tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, fslot);
+#if TRT_TAIL_DIAG >= 2
+                if (saw_dry) {                                 // the last 250 pixels to finish: who, how long, from when to when
+                    unsigned long long t;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                    const unsigned long long i = atomicAdd(&fp.stats[3], 1ull) % 250ull;
+                    fp.stats[520 + 2 * i] = (unsigned long long)xy | ((unsigned long long)target << 32);
+                    fp.stats[521 + 2 * i] = (((t_pix - t_base) / 100000ull) << 32) | ((t - t_base) / 100000ull);
+                }
+#endif
                 mode = NM_NEED_PIXEL;
             } else {
                 new_ray = true;
@@ -190,6 +212,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     target = fp.base_samples;
                     extra_phase = false;
                     new_ray = true;
+#if TRT_TAIL_DIAG >= 2
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_pix));
+#endif
                 } else {
                     mode = NM_DONE;
                 }
@@ -205,6 +230,15 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             mode = NM_ACTIVE;
         }
         // (the cooperative scan of SrcTiled needs every warp of the CTA in every iteration: leave together)
+#if TRT_TAIL_DIAG
+        if (!saw_dry && __any_sync(0xffffffffu, mode == NM_DONE)) {
+            saw_dry = true;
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            const unsigned long long b = (t - t_base) / 500000ull;
+            if (lane == 0 && TRT_TAIL_DIAG < 2) atomicAdd(&fp.stats[520 + (b < 511ull ? b : 511ull)], 1ull);
+        }
+#endif
         if (SRC::kTiled ? __syncthreads_and(mode == NM_DONE) : __all_sync(0xffffffffu, mode == NM_DONE)) break;
 
         // ---- this iteration's scan: queued light samples (when enough have queued up, or lanes are waiting for
@@ -429,7 +463,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         if (hit) {
             float3 s;
             if (mc.w > rnd(rng)) s = V::reflect(rd, hn);
-            else s = tr.cosine_hemisphere(rng, hn);
+            else s = tr.cosine_hemisphere_unit(rng, hn);
             att = V::mulv(att, xyz(mc));
             ro = V::axpy(hp, s, 0.001f);
             rd = s;
@@ -443,6 +477,14 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         }
         if (path_end) mode = NM_WAIT;
     }
+#if TRT_TAIL_DIAG
+    {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        const unsigned long long b = (t - t_base) / 500000ull;
+        if (lane == 0) atomicAdd(&fp.stats[8 + (b < 511ull ? b : 511ull)], 1ull);
+    }
+#endif
     tr.flush_stats();
 }
 

@@ -6,6 +6,9 @@
 #include <cuda_pipeline.h>
 #endif
 
+#ifndef TRT_TAIL_DIAG
+#define TRT_TAIL_DIAG 0  // measurement build (tools/tail_hist.py): 1 = histograms of when warps run dry / leave, 2 = last pixels
+#endif
 namespace trt {
 
 struct LightView {               // emissive spheres / triangles in scan order (shader.wgsl:342-392)
@@ -534,15 +537,16 @@ struct Tracer {
             const float nan = __int_as_float(0x7fc00000);
             const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
                                   fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
+            const float3 roi = V::mulv(ro, inv);
 #pragma unroll
             for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NP : TRT_STATIC_P); j++) {
                 if (j < n_pl) {
                     const float4 p = c_small.pl_p[j];
                     const int kind = SHAPE::kFixed ? SHAPE::kind(j) : __float_as_int(p.w);
                     float t;
-                    if (kind == 0) t = (p.x - ro.x) * inv.x;
-                    else if (kind == 1) t = (p.y - ro.y) * inv.y;
-                    else if (kind == 2) t = (p.z - ro.z) * inv.z;
+                    if (kind == 0) t = __fmaf_rn(p.x, inv.x, -roi.x);          // (p - o) / d as p * (1/d) - o * (1/d)
+                    else if (kind == 1) t = __fmaf_rn(p.y, inv.y, -roi.y);
+                    else if (kind == 2) t = __fmaf_rn(p.z, inv.z, -roi.z);
                     else {
                         const float3 n = xyz(c_small.pl_n[j]);
                         const float denom = V::dot(n, rd);
@@ -604,6 +608,10 @@ struct Tracer {
     __device__ __forceinline__ float3 normal_at(int i, int type, float3 p) const {
         if (type == 0) {
             float4 a = __ldg(&sc.ga[i]);
+            if (CONV == 2) {                                    // (p - c) / r normalised: only the sign of r survives
+                const float3 d = V::sub(p, xyz(a));
+                return V::scale(d, copysignf(rsqrt_native(V::dot(d, d)), a.w));
+            }
             return V::normalize(V::divs(V::sub(p, xyz(a)), a.w));
         }
         if (type >= 1 && type <= 8) return xyz(__ldg(&sc.gn[i]));
@@ -632,6 +640,29 @@ struct Tracer {
         float3 u = V::normalize(V::cross(f3(use_y ? 0.0f : 1.0f, use_y ? 1.0f : 0.0f, 0.0f), w));
         float3 v = V::cross(w, u);
         return V::normalize(V::lin3(u, x, v, y, w, z));
+    }
+
+    // conv 2 form of the same function for a UNIT normal (the hit record's): the re-normalisation of w is a
+    // rounding-level no-op, the helper axis is (0,1,0) or (1,0,0), so u = helper x w has one zero component and
+    // v = w x u one component equal to |helper x w|: written out (the x <-> y mirror image serves the second
+    // helper), the frame costs one rsqrt instead of two normalisations and two cross products.
+    __device__ __forceinline__ float3 cosine_hemisphere_unit(uint32_t &rng, float3 w) {
+        const float r1 = rnd(rng), r2 = rnd(rng);
+        const float cos_theta = sqrt_native(r1);
+        const float sin_theta = sqrt_native(1.0f - r1);
+        float sp, cp;
+        sincos_turn<2>(r2, sp, cp);
+        const float y = sin_theta * sp, z = cos_theta;
+        const bool use_y = fabsf(w.x) > 0.1f;
+        const float x = use_y ? sin_theta * cp : -(sin_theta * cp);
+        const float wx = use_y ? w.x : w.y, wy = use_y ? w.y : w.x;        // mirrored frame for the x helper
+        const float n2 = __fmaf_rn(w.z, w.z, wx * wx);
+        const float inv = rsqrt_native(n2);
+        const float a = w.z * inv, b = wx * inv, nn = n2 * inv, t = wy * y;
+        const float dx = __fmaf_rn(wx, z, __fmaf_rn(-b, t, a * x));
+        const float dy = __fmaf_rn(wy, z, nn * y);
+        const float dz = __fmaf_rn(w.z, z, __fmaf_rn(-a, t, -(b * x)));
+        return V::normalize(f3(use_y ? dx : dy, use_y ? dy : dx, dz));
     }
 
     // shader.wgsl:338-436.  The loop runs over the precomputed list of emissive spheres/triangles

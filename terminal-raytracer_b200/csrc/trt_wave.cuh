@@ -278,7 +278,9 @@ static inline cudaError_t wave_trace_launch(const SceneView &sv, const LightView
     if (e != cudaSuccess) return e;
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     const uint32_t want = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
-    const uint32_t cap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
+    // resident CTAs per SM: the caller's hint for short frames (trt_api.cu frame_ctas_hint), else all that fit
+    const uint32_t ctas = fp.ctas_hint >= 1u && fp.ctas_hint < TRT_WV_CTAS_PER_SM ? fp.ctas_hint : TRT_WV_CTAS_PER_SM;
+    const uint32_t cap = (uint32_t)sm_count * ctas;
     const uint32_t blocks = want < cap ? want : cap;
 #define TRT_WV_LAUNCH(CONV_, SRC_)                                                                                  \
     do {                                                                                                            \

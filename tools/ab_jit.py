@@ -8,13 +8,13 @@ S = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "t
 sc = json.load(open(os.path.join(S, {"scene2": "scene2.json", "demo": "demo.json"}.get(which, "Cornell_Box.json"))))
 if which == "cornell_swapped":
     sc["planes"] = sc["planes"][2:] + sc["planes"][:2]
-w, h, spp, depth = 1920, 1080, 64, 32
+w, h, spp, depth = 1920, 1080, int(sys.argv[2]) if len(sys.argv) > 2 else 64, 32
 prims = O.flatten_scene(sc)
 u = pkg.api.uniforms_from_bytes(O.make_uniforms(sc, len(prims), O.C1_SEED, 0, width=w, height=h, spp=spp, max_depth=depth).tobytes())
 r = pkg.Renderer(w, h, conv=2)
 t0 = time.perf_counter(); r.upload_scene(prims); r.render_frame(u, pkg.MODE_NONE); first = time.perf_counter() - t0
 best = 1e9
-for k in range(3):
+for k in range(5):
     r.render_frame(u, pkg.MODE_NONE); best = min(best, r.timings().trace_ms)
 st = r.frame_stats()
-print(f"{which}: {r.kernel_name()}: trace {best:.2f} ms, {st.samples_traced / best / 1e3:.1f} Msamples/s, {st.bounces / st.samples_traced:.2f} bounces/sample; first frame incl. upload/compile {first * 1e3:.0f} ms", flush=True)
+print(f"{os.environ.get('TRT_B200_JIT_DEFS', '')} {which}: {r.kernel_name()}: trace {best:.2f} ms, {st.samples_traced / best / 1e3:.1f} Msamples/s, {st.bounces / st.samples_traced:.2f} bounces/sample; first frame incl. upload/compile {first * 1e3:.0f} ms", flush=True)
