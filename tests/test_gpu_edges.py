@@ -169,3 +169,28 @@ def test_tile_boundaries_of_the_cooperative_scan(pkg, O, n_tris):
     sc["spheres"] += [{"center": [float(-3 + 0.05 * i), -0.5, -6.0], "radius": 0.02, "color": [0.5, 0.5, 0.5], "emission": [0, 0, 0],
                        "reflectivity": 0.0} for i in range(130)]
     _both(pkg, O, sc, 40, 20)
+
+
+def test_resident_cta_hint_changes_nothing_but_the_schedule(pkg, O):
+    """The second frame of a size is launched with fewer resident CTAs when the first one's bounce count says the
+    frame is short against its longest possible pixel (trt_api.cu frame_ctas_hint; here 640 x 240 pixels, 8 spp,
+    depth 8: more CTAs wanted than 7 per SM, R > 0.5).  Scheduling only: the strict frames are bit-identical, the
+    native ones agree to rounding (the order of a sample's light contributions is not fixed)."""
+    sc = json.load(open(os.path.join(SCENES, "Cornell_Box.json")))
+    sc = dict(sc, samples_per_pixel=8, max_depth=8)
+    prims = O.flatten_scene(sc)
+    w, h = 640, 240
+    u = O.make_uniforms(sc, len(prims), 7, 0, width=w, height=h)
+    for conv in (0, 2):
+        r = pkg.Renderer(w, h, conv=conv)
+        r.upload_scene(prims)
+        frames = []
+        for _ in range(3):
+            r.render_frame(_u(pkg, u), pkg.MODE_NONE)
+            frames.append(r.read_pixels().copy())
+        r.close()
+        if conv == 0:
+            assert np.array_equal(_bits(frames[0]), _bits(frames[1])) and np.array_equal(_bits(frames[0]), _bits(frames[2]))
+        else:
+            for f in frames[1:]:
+                assert _rel_bad(f.reshape(-1, 4)[:, :3], frames[0].reshape(-1, 4)[:, :3], 1e-5) == 0
