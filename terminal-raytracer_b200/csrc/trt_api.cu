@@ -89,6 +89,7 @@ struct trt_ctx {
     cudaEvent_t ev_stats = nullptr;
     bool stats_valid = false;
     uint32_t stats_w = 0, stats_h = 0, stats_pixels = 0, stats_spp = 0, stats_depth = 0;
+    uint64_t stats_bounces = 0;        // bounce count of the latest completed frame of that description
 
     trt_uniforms last_u{};
     bool have_frame = false;
@@ -435,8 +436,10 @@ static int check_uniforms(trt_ctx *ctx, const trt_uniforms *u) {
 static uint32_t frame_ctas_hint(trt_ctx *ctx, const FrameParams &fp) {
     if (!ctx->stats_valid || ctx->stats_w != fp.width || ctx->stats_h != fp.height || ctx->stats_pixels != fp.n_local_pixels ||
         ctx->stats_spp != fp.spp || ctx->stats_depth != fp.max_depth) return 0u;
-    if (cudaEventQuery(ctx->ev_stats) != cudaSuccess) { cudaGetLastError(); return 0u; }
-    const double bounces = (double)ctx->h_len[5];
+    // the latest frame whose statistics have arrived (frames may be queued faster than they complete)
+    if (cudaEventQuery(ctx->ev_stats) == cudaSuccess) ctx->stats_bounces = ctx->h_len[5];
+    else cudaGetLastError();
+    const double bounces = (double)ctx->stats_bounces;
     if (!(bounces > 0.0)) return 0u;
     const double lanes = (double)ctx->sm_count * 8.0 * 128.0;
     const double r = (double)fp.spp * (double)(fp.max_depth ? fp.max_depth : 1u) * lanes / bounces;
@@ -524,6 +527,9 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
         if (!ctx->ev_stats) CK(cudaEventCreateWithFlags(&ctx->ev_stats, cudaEventDisableTiming));
         CK(cudaMemcpyAsync(ctx->h_len + 4, ctx->d_stats, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaEventRecord(ctx->ev_stats, ctx->stream));
+        if (!(ctx->stats_valid && ctx->stats_w == u->width && ctx->stats_h == u->height && ctx->stats_pixels == fp.n_local_pixels &&
+              ctx->stats_spp == fp.spp && ctx->stats_depth == fp.max_depth))
+            ctx->stats_bounces = 0;                       // a different frame description: no history yet
         ctx->stats_valid = true;
         ctx->stats_w = u->width; ctx->stats_h = u->height; ctx->stats_pixels = fp.n_local_pixels;
         ctx->stats_spp = fp.spp; ctx->stats_depth = fp.max_depth;
