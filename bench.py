@@ -221,7 +221,7 @@ def ours(args):
     if rank == 0:
         sampler.start()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    trace_ms, samples_local, launches = [], 0, 0
+    trace_ms, combine_ms, samples_local, launches = [], [], 0, 0
     barrier()
     for k in range(args.steps):
         if flush is not None:
@@ -232,7 +232,9 @@ def ours(args):
         evs[k][1].record(stream)
         # per-step statistics are read back after the step's stop event (they sync the stream)
         t = sr.r.timings()
-        trace_ms.append(t.trace_ms)
+        st = sr.step_times()                          # this rank's trace kernel alone / pack + gather / quantise
+        trace_ms.append(st[0])
+        combine_ms.append(st[1] + st[2])
         launches += t.kernel_launches                 # trace + pack_rows + 3 quantise kernels (rank 0)
         samples_local += sr.r.frame_stats().samples_traced
     barrier()
@@ -245,8 +247,15 @@ def ours(args):
         sm = tt.clone()
         dist.all_reduce(sm, op=dist.ReduceOp.SUM)
         dev_ms, samples_total, trace_sum_max = mx[0].item(), sm[1].item(), mx[2].item()
+        per_rank = [torch.zeros(2, dtype=torch.float64, device=f"cuda:{local}") for _ in range(world)]
+        dist.all_gather(per_rank, torch.tensor([sum(trace_ms) / args.steps, sum(combine_ms) / args.steps], dtype=torch.float64,
+                                               device=f"cuda:{local}"))
+        ranks = {"trace_ms": [round(v[0].item(), 2) for v in per_rank],
+                 "combine_ms_rank0": round(per_rank[0][1].item(), 2),
+                 "note": "per rank: its trace kernel alone; rank 0: pack + gather (waits for the slowest rank) + quantise"}
     else:
         samples_total, trace_sum_max = float(samples_local), float(sum(trace_ms))
+        ranks = None
 
     # ---- end to end through trt_render_frame with host buffers (rank-local frame; N = 1 only is exact) ---
     e2e = None
@@ -367,6 +376,8 @@ def ours(args):
                        "l2": "256 MiB flush between timed steps" if small else "frame buffers (3 x %d MB) exceed the 126 MB L2" % (frame_bytes >> 20),
                        "parallelism": f"rows x{world}"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "strict": strict}
+    if ranks:
+        line["ranks"] = ranks
     print(json.dumps(line), flush=True)
     sr.close()
     if world > 1:

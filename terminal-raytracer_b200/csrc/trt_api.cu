@@ -494,7 +494,12 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
         ctx->launches += 1;
         fp.order = ctx->d_order;
     }
-    if (!n_batch) fp.ctas_hint = frame_ctas_hint(ctx, fp);
+    if (!n_batch) {
+        fp.ctas_hint = frame_ctas_hint(ctx, fp);
+        static const bool say = [] { const char *k = getenv("TRT_B200_VERBOSE"); return k && *k == '1'; }();
+        if (say) fprintf(stderr, "[trt_b200] frame %ux%u, %u local pixels: resident CTAs hint %u (bounces of the last frame %llu)\n", fp.width,
+                         fp.height, fp.n_local_pixels, fp.ctas_hint, (unsigned long long)ctx->stats_bounces);
+    }
     if (fp.n_local_pixels) {
         if (ctx->cfg.count_work) {
             const uint32_t blocks = (fp.n_local_pixels + 127u) / 128u;

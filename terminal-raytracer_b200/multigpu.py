@@ -55,6 +55,8 @@ class ShardedRenderer:
         dev = torch.device("cuda", device)
         self.block = torch.zeros(self.block_elems, dtype=torch.float32, device=dev)
         self.gathered = (torch.zeros(world * self.block_elems, dtype=torch.float32, device=dev) if rank == 0 else None)
+        # device time stamps of the last step: start, trace done, gather done, quantise done (step_times)
+        self.marks = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
 
     def upload_scene(self, prims):
         self.r.upload_scene(prims)
@@ -63,7 +65,9 @@ class ShardedRenderer:
         """Trace this rank's rows, gather to rank 0, quantise there.  Asynchronous on the context's stream."""
         torch, dist = self.torch, self.dist
         with torch.cuda.stream(self.stream):
+            self.marks[0].record(self.stream)
             self.r.trace_async(u)
+            self.marks[1].record(self.stream)
             self.r.pack_shard_pixels(self.block.data_ptr(), self.block.numel() * 4)
             if self.world > 1:
                 glist = list(self.gathered.view(self.world, self.block_elems).unbind(0)) if self.rank == 0 else None
@@ -71,9 +75,17 @@ class ShardedRenderer:
                 src = self.gathered
             else:
                 src = self.block
+            self.marks[2].record(self.stream)
             if self.rank == 0 and mode != self.pkg.MODE_NONE:
                 self.r.quantise_gathered(src.data_ptr(), self.block_elems * 4, self.w, self.h, self.world, self.stripe,
                                          mode, want_len=False)
+            self.marks[3].record(self.stream)
+
+    def step_times(self):
+        """(trace, pack + gather incl. waiting for the slowest rank, quantise) of the last step in ms; synchronises."""
+        self.marks[3].synchronize()
+        m = self.marks
+        return m[0].elapsed_time(m[1]), m[1].elapsed_time(m[2]), m[2].elapsed_time(m[3])
 
     def close(self):
         self.r.close()
