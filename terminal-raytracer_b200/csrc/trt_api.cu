@@ -57,6 +57,8 @@ struct trt_ctx {
     unsigned int *d_work = nullptr;
     unsigned long long *d_stats = nullptr;
     uint32_t *d_order = nullptr;       // hand-out order of the local pixels (longest first)
+    uint32_t *d_cost = nullptr;        // bounces per pixel of the last frame (production kernel), valid when cost_valid
+    bool cost_valid = false, cost_kernel = false;
     uint32_t order_w = 0, order_h = 0; // frame size the variance buffer was last written for (0: no history)
     uint32_t *d_row_map = nullptr;     // local row -> global row
     uint64_t *d_row_src = nullptr;     // quantiser source offsets per output row
@@ -123,7 +125,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_tiles, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
                     ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
-                    ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream};
+                    ctx->d_cost, ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
     if (ctx->h_batch_len) cudaFreeHost(ctx->h_batch_len);
@@ -175,6 +177,7 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         CK(cudaMalloc(&ctx->d_stats, TRT_STATS_BYTES));
         CK(cudaMemsetAsync(ctx->d_stats, 0, TRT_STATS_BYTES, ctx->stream));
         CK(cudaMalloc(&ctx->d_order, ctx->max_pixels * sizeof(uint32_t)));
+        CK(cudaMalloc(&ctx->d_cost, ctx->max_pixels * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_map, (size_t)cfg->max_height * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_src, (size_t)cfg->max_height * sizeof(uint64_t)));
         CK(cudaMalloc(&ctx->d_packed, ctx->max_pixels * sizeof(uint32_t)));
@@ -486,10 +489,12 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     if (!no_order && !n_batch && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
         CK(cudaMemsetAsync(ctx->d_work + 16, 0, 2 * TRT_ORDER_BUCKETS * sizeof(unsigned int), ctx->stream));
         const uint32_t ob = (fp.n_local_pixels + 255u) / 256u;
+        const uint32_t *cost = ctx->cost_valid ? ctx->d_cost : nullptr;
+        const float max_cost = (float)fp.spp * (float)(fp.max_depth ? fp.max_depth : 1u);
         order_count_kernel<<<ob, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width, fp.n_local_pixels, fp.base_samples,
-                                                       fp.spp, ctx->d_work + 16);
+                                                       fp.spp, ctx->d_work + 16, cost, max_cost);
         order_scatter_kernel<<<ob, 256, 0, ctx->stream>>>(ctx->d_variance, fp.row_map, fp.width, fp.n_local_pixels, fp.base_samples,
-                                                         fp.spp, ctx->d_work + 16, ctx->d_order);
+                                                         fp.spp, ctx->d_work + 16, ctx->d_order, cost, max_cost);
         ctx->launches += 1;
         ctx->launches += 1;
         fp.order = ctx->d_order;
@@ -509,9 +514,11 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
             ctx->kernel_name = "trace_pixel_kernel<CONV, count>";
             ctx->launches += 1;
         } else if (ctx->cfg.conv == 2u) {
+            if (!n_batch) fp.cost = ctx->d_cost;
             cudaError_t e = native_trace_launch(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, &ctx->small, fp, ctx->sm_count,
                                                 ctx->stream, &ctx->launches, &ctx->kernel_name);
             if (e != cudaSuccess) { ctx->err = std::string("native trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
+            ctx->cost_kernel = strstr(ctx->kernel_name, "native") || strstr(ctx->kernel_name, "jit");   // the wave fallback records no cost
         } else {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
             // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)
@@ -543,6 +550,7 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     ctx->have_frame = true;
     ctx->order_w = u->width;
     ctx->order_h = u->height;
+    ctx->cost_valid = fp.cost != nullptr && fp.n_local_pixels != 0u && ctx->cost_kernel;
     return TRT_OK;
 }
 

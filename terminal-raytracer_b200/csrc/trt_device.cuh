@@ -67,6 +67,9 @@ struct FrameParams {
     float4 *batch_cur;
     uint32_t n_batch;
     uint32_t ctas_hint;             // host only: resident CTAs per SM the launcher should use (0: all that fit)
+    // bounce count of every pixel of this frame (global pixel index), written by the production kernel: the measured
+    // length of the pixel's serial chain, which orders the next frame's hand-out (order_*_kernel); NULL: not recorded
+    uint32_t *cost;
 };
 
 // shader.wgsl:610-619: the temporal blend of one pixel, with explicit roundings so that every call site

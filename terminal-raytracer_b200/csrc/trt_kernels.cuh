@@ -97,10 +97,18 @@ __global__ void __launch_bounds__(128) trace_pixel_kernel(SceneView sc, LightVie
 // (bit-identical frames).  order_count_kernel builds the histogram, order_scatter_kernel places the pixels
 // (order inside a class is arbitrary).
 #define TRT_ORDER_BUCKETS 32
+// With `cost` (the bounce count the production kernel measured for every pixel of the previous frame) the classes are
+// eighth-octaves of the measured chain length below max_cost = spp * max_depth: what bounds a short frame is its
+// longest chains (deep paths x many samples), which the sample count alone does not tell.
 __device__ __forceinline__ uint32_t order_bucket(const trt_variance *variance, const uint32_t *row_map, uint32_t width, uint32_t lp,
-                                                 uint32_t base_samples, uint32_t spp) {
+                                                 uint32_t base_samples, uint32_t spp, const uint32_t *cost, float max_cost) {
     const uint32_t lr = lp / width, x = lp - lr * width;
     const uint32_t y = row_map ? row_map[lr] : lr;
+    if (cost) {
+        const float c = fmaxf(1.0f, (float)cost[(size_t)y * width + x]);
+        const float b = 8.0f * log2f(fmaxf(1.0f, max_cost / c));
+        return min((uint32_t)b, (uint32_t)TRT_ORDER_BUCKETS - 1u);                               // bucket 0 = longest
+    }
     const float v = variance[(size_t)y * width + x].variance;
     uint32_t predicted = base_samples;
     if (v > 10.0f && base_samples < spp) predicted += min(spp - base_samples, __float2uint_rz(v * 50.0f));
@@ -108,19 +116,20 @@ __device__ __forceinline__ uint32_t order_bucket(const trt_variance *variance, c
     return (TRT_ORDER_BUCKETS - 1u) - min(cls, (uint32_t)TRT_ORDER_BUCKETS - 1u);        // bucket 0 = longest
 }
 static __global__ void order_count_kernel(const trt_variance *variance, const uint32_t *row_map, uint32_t width,
-                                          uint32_t n_local_pixels, uint32_t base_samples, uint32_t spp, unsigned int *hist) {
+                                          uint32_t n_local_pixels, uint32_t base_samples, uint32_t spp, unsigned int *hist,
+                                          const uint32_t *cost, float max_cost) {
     __shared__ unsigned int sh[TRT_ORDER_BUCKETS];
     if (threadIdx.x < TRT_ORDER_BUCKETS) sh[threadIdx.x] = 0u;
     __syncthreads();
     const uint32_t lp = blockIdx.x * blockDim.x + threadIdx.x;
-    if (lp < n_local_pixels) atomicAdd(&sh[order_bucket(variance, row_map, width, lp, base_samples, spp)], 1u);
+    if (lp < n_local_pixels) atomicAdd(&sh[order_bucket(variance, row_map, width, lp, base_samples, spp, cost, max_cost)], 1u);
     __syncthreads();
     if (threadIdx.x < TRT_ORDER_BUCKETS && sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], sh[threadIdx.x]);
 }
 // hist[0..B) = class sizes, hist[B..2B) = cursors (zeroed by the host)
 static __global__ void order_scatter_kernel(const trt_variance *variance, const uint32_t *row_map, uint32_t width,
                                             uint32_t n_local_pixels, uint32_t base_samples, uint32_t spp, unsigned int *hist,
-                                            uint32_t *order) {
+                                            uint32_t *order, const uint32_t *cost, float max_cost) {
     __shared__ unsigned int cnt[TRT_ORDER_BUCKETS], start[TRT_ORDER_BUCKETS], base[TRT_ORDER_BUCKETS];
     if (threadIdx.x < TRT_ORDER_BUCKETS) cnt[threadIdx.x] = 0u;
     __syncthreads();
@@ -128,7 +137,7 @@ static __global__ void order_scatter_kernel(const trt_variance *variance, const 
     uint32_t b = 0, rank = 0;
     const bool live = lp < n_local_pixels;
     if (live) {
-        b = order_bucket(variance, row_map, width, lp, base_samples, spp);
+        b = order_bucket(variance, row_map, width, lp, base_samples, spp, cost, max_cost);
         rank = atomicAdd(&cnt[b], 1u);
     }
     __syncthreads();

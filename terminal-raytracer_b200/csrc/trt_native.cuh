@@ -96,6 +96,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     __shared__ float s_ring[TRT_NV_THREADS / 32][DQ_FIELDS][TRT_NV_RING];
     __shared__ float s_late[3][TRT_NV_THREADS];
     __shared__ unsigned s_res[TRT_NV_THREADS];
+    __shared__ uint32_t s_b0[TRT_NV_THREADS];    // the lane's bounce counter when its pixel began (-> fp.cost)
     __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
     // SrcTiled: second FIFO, of ready shadow rays (origin, direction, contribution, t_max in DQ_RNG, owner in DQ_META)
     __shared__ float s_rays[SRC::kTiled ? TRT_NV_THREADS / 32 : 1][DQ_FIELDS][SRC::kTiled ? TRT_NV_RING : 1];
@@ -167,6 +168,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             if (finished) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
                 tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, fslot);
+                if (fp.cost) fp.cost[(size_t)(xy >> 16) * fp.width + (xy & 0xffffu)] = tr.n_bounces - s_b0[tid];
 #if TRT_TAIL_DIAG >= 2
                 if (saw_dry) {                                 // the last 250 pixels to finish: who, how long, from when to when
                     unsigned long long t;
@@ -212,6 +214,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     target = fp.base_samples;
                     extra_phase = false;
                     new_ray = true;
+                    s_b0[tid] = tr.n_bounces;
 #if TRT_TAIL_DIAG >= 2
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_pix));
 #endif
