@@ -5,6 +5,8 @@
 #include <cstring>
 #include <cmath>
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -365,7 +367,7 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     ctx->lv.la = rp.la; ctx->lv.lb = rp.lb; ctx->lv.lc = rp.lc; ctx->lv.ln = rp.ln; ctx->lv.le = rp.le;
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->have_scene = true;
-    static unsigned long long g_scene_serial = 0;     // process-wide: a recycled ctx address never aliases
+    static std::atomic<unsigned long long> g_scene_serial{0};     // process-wide: a recycled ctx address never aliases
     ctx->scene_serial = ++g_scene_serial;
     return TRT_OK;
 }
@@ -449,6 +451,12 @@ static uint32_t frame_ctas_hint(trt_ctx *ctx, const FrameParams &fp) {
     return r < 0.5 ? 0u : r < 2.5 ? 7u : 6u;
 }
 
+// State shared by every context of the process: the per-device __constant__ scene mirrors with their owners
+// (trt_persistent.cuh, trt_native.cu) and the cache of run-time compiled kernels (trt_jit.cuh).  Binding a scene and
+// launching its frame is one critical section, so contexts owned by different host threads can render side by side
+// (a context itself stays single-owner, include/trt_b200.h); the kernels run asynchronously outside the lock.
+static std::mutex g_device_state_mutex;
+
 static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     int rc = check_uniforms(ctx, u);
     if (rc) return rc;
@@ -467,6 +475,9 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     fp.half_w = u->aspect_ratio * fp.half_h;             // shader.wgsl:523
     fp.wm1 = (float)(u->width - 1u);
     fp.hm1 = (float)(u->height - 1u);
+    fp.cam_kx = 2.0f * fp.half_w / fp.wm1;
+    fp.cam_ky = 2.0f * fp.half_h / (fp.hm1 * fp.char_aspect);
+    fp.cam_cy = fp.half_h / fp.char_aspect;
     fp.spp_f = (float)u->samples_per_pixel;
     fp.base_f = (float)fp.base_samples;
     fp.cam_pos = make_float3(u->camera_pos.x, u->camera_pos.y, u->camera_pos.z);
@@ -506,6 +517,7 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
                          fp.height, fp.n_local_pixels, fp.ctas_hint, (unsigned long long)ctx->stats_bounces);
     }
     if (fp.n_local_pixels) {
+        std::lock_guard<std::mutex> lock(g_device_state_mutex);
         if (ctx->cfg.count_work) {
             const uint32_t blocks = (fp.n_local_pixels + 127u) / 128u;
             // the work counters are those of the as-written shader: conv 2 contexts count with conv 0 arithmetic

@@ -52,6 +52,9 @@ struct FrameParams {
     float inv_unused, char_aspect, half_h, half_w;      // half_h = tan(fov/2) (host, glibc), half_w = aspect*half_h
     float wm1, hm1;                                     // f32(width-1), f32(height-1)
     float spp_f, base_f;
+    // conv 2 camera ray with the frame-uniform factors folded on the host (TRT_V_CAMFOLD): view-plane coordinates
+    // vx = (x + r) * cam_kx - half_w, vy = (height-1-y + r) * cam_ky - cam_cy  (shader.wgsl:519-531 multiplied out)
+    float cam_kx, cam_ky, cam_cy;
     float3 cam_pos, cam_fwd, cam_right, cam_up;
     const uint32_t *row_map;     // local row -> global row (row sharding); NULL = identity
     const uint32_t *order;       // hand-out order of the local pixels (longest first, from the previous frame's variance); NULL = natural
@@ -189,11 +192,21 @@ template <int CONV> struct M {
     }
 };
 
+#ifndef TRT_V_PCG_MULHI
+#define TRT_V_PCG_MULHI 0   // measured: slower (IMAD.HI is no cheaper than the shift), kept off
+#endif
 // ---- RNG (shader.wgsl:104-115) --------------------------------------------------------------------
 __device__ __forceinline__ uint32_t pcg_hash(uint32_t input) {
     uint32_t state = input * 747796405u + 2891336453u;
     uint32_t word = ((state >> ((state >> 28u) + 4u)) ^ state) * 277803737u;
+#if TRT_V_PCG_MULHI
+    // word >> 22 as the high half of word * 2^10: the same bits from the multiplier pipe instead of the ALU pipe
+    uint32_t hi;
+    asm("mul.hi.u32 %0, %1, 1024;" : "=r"(hi) : "r"(word));
+    return hi ^ word;
+#else
     return (word >> 22u) ^ word;
+#endif
 }
 // f32(state) / 4294967295.0: the literal is 2^32 in f32, so this is an exact scaling by 2^-32
 __device__ __forceinline__ float rnd(uint32_t &state) {

@@ -37,6 +37,30 @@ namespace trt {
 #ifndef TRT_NV_CTAS_PER_SM
 #define TRT_NV_CTAS_PER_SM 8
 #endif
+// guarded variants (A/B through TRT_B200_JIT_DEFS / the Makefile's VARIANTS):
+// TRT_V_EXTRA_NOWAIT: an adaptive extra sample only adds to the pixel's sum (shader.wgsl:596), so it is finished
+//   without waiting for its queued light samples; they land in the lane's late sum until the pixel's last sample,
+//   which waits for all of them (the sum of squares of the base samples still needs every sample complete);
+// TRT_NV_WAIT_W: weight of a waiting lane in the flush rule of the queue
+#ifndef TRT_V_EXTRA_NOWAIT
+#define TRT_V_EXTRA_NOWAIT 1
+#endif
+#ifndef TRT_NV_WAIT_W
+#define TRT_NV_WAIT_W 1
+#endif
+// TRT_X_NOWAIT_ALL (measurement only, never shipped on): every sample but a pixel's last is finished without
+//   waiting -- the upper bound of what parking can gain (the variance is then wrong);
+// TRT_NV_SLOTS (power of two): a BASE sample whose light samples are still queued is parked in shared memory
+//   (its radiance so far, and the number of entries the lane had posted when it ended) and the lane starts the next
+//   sample; queue entries carry the sample's slot, so every parked sample has its own late sum.  Parked samples are
+//   closed in sample order as soon as their entries are resolved: the sums of :549-551 see the same values in the
+//   same order as without parking.  1 = no parking.
+#ifndef TRT_X_NOWAIT_ALL
+#define TRT_X_NOWAIT_ALL 0
+#endif
+#ifndef TRT_NV_SLOTS
+#define TRT_NV_SLOTS 4
+#endif
 #define TRT_NV_RING 64           // queued hits per warp: at most 31 left over + 32 new ones per iteration
 #define TRT_NV_MAX_LIGHTS 16     // light mask bits in the entry's meta word
 
@@ -94,7 +118,15 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     Counters<false> cn;
     Tracer<2, false, SRC> tr(sc, lv, fp, cn);
     __shared__ float s_ring[TRT_NV_THREADS / 32][DQ_FIELDS][TRT_NV_RING];
-    __shared__ float s_late[3][TRT_NV_THREADS];
+    // Parking needs the queue to resolve a lane's entries in the order they were posted (the small-scene queue does:
+    // an entry is resolved whole, at its last light).  The two-stage queue of SrcTiled resolves a light sample that
+    // is not needed on the spot, ahead of older samples still in the ray FIFO: no parking there (one slot).
+    constexpr unsigned kSlots = SRC::kTiled ? 1u : (unsigned)TRT_NV_SLOTS;
+    __shared__ float s_late[kSlots][3][TRT_NV_THREADS];
+#if TRT_NV_SLOTS > 1
+    __shared__ float s_park[kSlots][3][TRT_NV_THREADS];          // radiance of a parked sample before its late sum
+    __shared__ unsigned s_mark[kSlots][TRT_NV_THREADS];          // entries the lane had posted when that sample ended
+#endif
     __shared__ unsigned s_res[TRT_NV_THREADS];
     __shared__ uint32_t s_b0[TRT_NV_THREADS];    // the lane's bounce counter when its pixel began (-> fp.cost)
     __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
@@ -104,9 +136,15 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     const unsigned lt_mask = (1u << lane) - 1u;
     float (*ring)[TRT_NV_RING] = s_ring[tid >> 5];
     float (*rays)[SRC::kTiled ? TRT_NV_RING : 1] = s_rays[SRC::kTiled ? tid >> 5 : 0];
-    volatile float *late_x = &s_late[0][tid], *late_y = &s_late[1][tid], *late_z = &s_late[2][tid];
+    // the late sum of slot s, component c, of this lane: late[(3 * s + c) * TRT_NV_THREADS]
+    volatile float *late = &s_late[0][0][tid];
+#if TRT_NV_SLOTS <= 1
+    volatile float *late_x = late, *late_y = late + TRT_NV_THREADS, *late_z = late + 2 * TRT_NV_THREADS;
+#endif
     volatile unsigned *res = &s_res[tid];
-    *late_x = 0.0f; *late_y = 0.0f; *late_z = 0.0f; *res = 0u;
+#pragma unroll
+    for (int i = 0; i < 3 * (int)kSlots; i++) late[i * TRT_NV_THREADS] = 0.0f;
+    *res = 0u;
     __syncwarp();
 
     uint32_t head = 0, tail = 0;                 // FIFO counters, identical in every lane of the warp
@@ -118,6 +156,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     uint32_t pend = 0;                           // entries this lane has posted so far
     int mode = NM_NEED_PIXEL;
     uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0, fslot = 0;
+#if TRT_NV_SLOTS > 1
+    uint32_t fin = 0;                            // samples of the pixel closed so far; fin .. si - 1 are parked
+#endif
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     bool extra_phase = false;
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
@@ -142,12 +183,59 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         // ---- finish the sample of a lane whose path has ended and whose queue entries are all resolved ------
         // (shader.wgsl:548-551, :555-565, :596-621)
         bool new_ray = false;
-        if (mode == NM_WAIT && *res == pend) {
-            acc = V::add(acc, f3(*late_x, *late_y, *late_z));
-            *late_x = 0.0f; *late_y = 0.0f; *late_z = 0.0f;
+#if TRT_NV_SLOTS <= 1
+        const bool early = (TRT_X_NOWAIT_ALL || (TRT_V_EXTRA_NOWAIT && extra_phase)) && si + 1u != target;
+        if (mode == NM_WAIT && (early || *res == pend)) {
+            if (!early) {
+                acc = V::add(acc, f3(*late_x, *late_y, *late_z));
+                *late_x = 0.0f; *late_y = 0.0f; *late_z = 0.0f;
+            }
             tr.n_samples++;
             pixel_color = V::add(pixel_color, acc);
             if (!extra_phase) sq_sum = V::add(sq_sum, V::mulv(acc, acc));
+#else
+        bool retire = false;
+        if (mode == NM_WAIT) {
+            const unsigned r = *res;
+            // parked samples whose entries have all been resolved, oldest first
+            while (fin != si) {
+                const unsigned ps = fin & (kSlots - 1u);
+                if ((int)(r - s_mark[ps][tid]) < 0) break;
+                volatile float *pl = late + 3u * ps * TRT_NV_THREADS;
+                const float3 a = f3(s_park[ps][0][tid] + pl[0], s_park[ps][1][tid] + pl[TRT_NV_THREADS],
+                                    s_park[ps][2][tid] + pl[2 * TRT_NV_THREADS]);
+                pl[0] = 0.0f; pl[TRT_NV_THREADS] = 0.0f; pl[2 * TRT_NV_THREADS] = 0.0f;
+                pixel_color = V::add(pixel_color, a);
+                sq_sum = V::add(sq_sum, V::mulv(a, a));
+                fin++;
+            }
+            // the sample that has just ended: an extra sample only adds to the pixel's sum (:596) and its light samples
+            // may arrive until the pixel's last sample (all in slot 0); a base sample is closed if nothing is
+            // outstanding, else parked if a slot is free for the next one; the last sample of a phase waits
+            const unsigned cs = extra_phase ? 0u : si & (kSlots - 1u);
+            const bool last = si + 1u == target;
+            if (extra_phase && !last) {
+                fin++;
+                retire = true;
+            } else if (fin == si && r == pend) {
+                volatile float *pl = late + 3u * cs * TRT_NV_THREADS;
+                acc = V::add(acc, f3(pl[0], pl[TRT_NV_THREADS], pl[2 * TRT_NV_THREADS]));
+                pl[0] = 0.0f; pl[TRT_NV_THREADS] = 0.0f; pl[2 * TRT_NV_THREADS] = 0.0f;
+                fin++;
+                retire = true;
+            } else if (!last && si + 1u - fin < kSlots) {
+                s_park[cs][0][tid] = acc.x; s_park[cs][1][tid] = acc.y; s_park[cs][2][tid] = acc.z;
+                s_mark[cs][tid] = pend;                        // its value joins the sums when it is closed
+                retire = true;
+            }
+        }
+        if (retire) {
+            tr.n_samples++;
+            if (fin == si + 1u) {                              // closed (not parked)
+                pixel_color = V::add(pixel_color, acc);
+                if (!extra_phase) sq_sum = V::add(sq_sum, V::mulv(acc, acc));
+            }
+#endif
             si++;
             bool finished = false;
             float variance_value = 0.0f;
@@ -211,6 +299,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     pixel_color = f3(0, 0, 0);
                     sq_sum = f3(0, 0, 0);
                     si = 0;
+#if TRT_NV_SLOTS > 1
+                    fin = 0;
+#endif
                     target = fp.base_samples;
                     extra_phase = false;
                     new_ray = true;
@@ -249,7 +340,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         bool spass = false, qvalid = false, qneed = false;
         float3 qo = ro, qd = rd, qc = f3(0, 0, 0);
         float qt = 1e10f;
-        unsigned qowner = 0, qrest = 0;
+        unsigned qowner = 0, qrest = 0, qslot = 0;
         uint32_t qrng = 0, qn = 0;
         const uint32_t qe = (head + lane) & (TRT_NV_RING - 1u);
         if (SRC::kTiled) {
@@ -268,8 +359,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 uint32_t erng = 0;
                 if (lane < en) {
                     const unsigned meta = __float_as_uint(ring[DQ_META][ee]);
-                    owner = meta & 0xffu;
-                    lmask = meta >> 8;
+                    owner = meta & 0xffu;                         // owner | slot << 8 travels on to the ray FIFO
+                    lmask = (meta >> 8) & 0xffffu;
+                    owner |= (meta >> 24) << 8;
                     erng = __float_as_uint(ring[DQ_RNG][ee]);
                 }
                 const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
@@ -289,7 +381,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     const float3 C = f3(ring[DQ_CX][ee], ring[DQ_CY][ee], ring[DQ_CZ][ee]);
                     needed = nee_sample<SHAPE>(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                         __uint2float_rn(erng) * 2.3283064365386963e-10f, so, sd, st, scn);
-                    if (!needed) atomicAdd(&s_res[owner], 1u);
+                    if (!needed) atomicAdd(&s_res[owner & 0xffu], 1u);
                 }
                 const unsigned mn = __ballot_sync(0xffffffffu, needed);
                 if (needed) {
@@ -324,6 +416,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     qc = f3(rays[DQ_CX][e], rays[DQ_CY][e], rays[DQ_CZ][e]);
                     qt = rays[DQ_RNG][e];
                     qowner = __float_as_uint(rays[DQ_META][e]);
+                    qslot = qowner >> 8;
+                    qowner &= 0xffu;
                     qneed = true;
                 }
             }
@@ -334,7 +428,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             if (sp_k < 0 && cnt > 0u) {
                 const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
                 const unsigned m_wait = __ballot_sync(0xffffffffu, mode == NM_WAIT);
-                if (cnt >= 32u || cnt + 2u * __popc(m_wait) >= 32u || !m_active) sp_k = 0;
+                if (cnt >= 32u || cnt + TRT_NV_WAIT_W * __popc(m_wait) >= 32u || !m_active) sp_k = 0;
             }
             spass = sp_k >= 0;
             qn = cnt < 32u ? cnt : 32u;
@@ -344,7 +438,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 if (qvalid) {
                     const unsigned meta = __float_as_uint(ring[DQ_META][qe]);
                     qowner = meta & 0xffu;
-                    lmask = meta >> 8;
+                    lmask = (meta >> 8) & 0xffffu;
+                    qslot = meta >> 24;
                     qrng = __float_as_uint(ring[DQ_RNG][qe]);
                 }
                 const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
@@ -380,9 +475,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         if (spass) {                                              // shader.wgsl:402-431 for the queued samples
             if (qvalid) {
                 if (t_hit < 0.0f && qneed) {
-                    atomicAdd(&s_late[0][qowner], qc.x);
-                    atomicAdd(&s_late[1][qowner], qc.y);
-                    atomicAdd(&s_late[2][qowner], qc.z);
+                    atomicAdd(&s_late[qslot][0][qowner], qc.x);
+                    atomicAdd(&s_late[qslot][1][qowner], qc.y);
+                    atomicAdd(&s_late[qslot][2][qowner], qc.z);
                 }
                 if (SRC::kTiled) atomicAdd(&s_res[qowner], 1u);
                 else if (qrest) ring[DQ_RNG][qe] = __uint_as_float(qrng);
@@ -455,7 +550,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 ring[DQ_NX][e] = hn.x; ring[DQ_NY][e] = hn.y; ring[DQ_NZ][e] = hn.z;
                 ring[DQ_CX][e] = mc.x * att.x; ring[DQ_CY][e] = mc.y * att.y; ring[DQ_CZ][e] = mc.z * att.z;
                 ring[DQ_RNG][e] = __uint_as_float(rng0);
-                ring[DQ_META][e] = __uint_as_float(tid | (lmask << 8));
+                // meta: owner thread | light mask << 8 | slot of the sample << 24 (extra samples: slot 0)
+                ring[DQ_META][e] = __uint_as_float(tid | (lmask << 8) | ((kSlots > 1u && !extra_phase ? si & (kSlots - 1u) : 0u) << 24));
                 pend += SRC::kTiled ? (uint32_t)__popc(lmask) : 1u;      // units to resolve: light samples / the entry
             }
             tail += __popc(mp);

@@ -161,6 +161,11 @@ __device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool
     return r;
 }
 
+// guarded kernel variants (A/B through TRT_B200_JIT_DEFS or the Makefile's VARIANTS)
+#ifndef TRT_V_CAMFOLD
+#define TRT_V_CAMFOLD 1
+#endif
+
 template <int CONV, bool COUNT, class SRC>
 struct Tracer {
     typedef M<CONV> V;
@@ -784,6 +789,19 @@ struct Tracer {
     // shader.wgsl:519-546
     __device__ __forceinline__ void camera_ray(uint32_t &rng, uint32_t x, uint32_t y, float3 &ro, float3 &rd) {
         if (COUNT) cn.add(K_RNG_DRAWS, 2);
+#if TRT_V_CAMFOLD
+        if (CONV == 2) {
+            // the same affine map with the frame-uniform divisions and products folded into three host constants
+            // (FrameParams::cam_kx/ky/cy): two fused multiply-adds per axis instead of :520-531's chain
+            const float px = __uint2float_rn(x) + rnd(rng);
+            const float py = __uint2float_rn(fp.height - 1u - y) + rnd(rng);
+            const float vx = __fmaf_rn(px, fp.cam_kx, -fp.half_w);
+            const float vy = __fmaf_rn(py, fp.cam_ky, -fp.cam_cy);
+            rd = V::normalize(V::axpy(V::axpy(fp.cam_fwd, fp.cam_up, vy), fp.cam_right, vx));
+            ro = fp.cam_pos;
+            return;
+        }
+#endif
         float u = (__uint2float_rn(x) + rnd(rng)) / fp.wm1;
         float v = (__uint2float_rn(fp.height - 1u - y) + rnd(rng)) / fp.hm1;
         float ndc_x = 2.0f * u - 1.0f;

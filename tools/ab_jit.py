@@ -17,4 +17,13 @@ best = 1e9
 for k in range(5):
     r.render_frame(u, pkg.MODE_NONE); best = min(best, r.timings().trace_ms)
 st = r.frame_stats()
+px = r.read_pixels().reshape(-1, 4)[:, :3].astype('float64')
+ref_path = os.environ.get("AB_REF")            # first run writes the frame, later runs report their RMSE against it
+if ref_path:
+    import numpy as np
+    if os.path.exists(ref_path):
+        ref = np.load(ref_path)
+        print(f"  vs {ref_path}: rmse {float(np.sqrt(((px - ref) ** 2).mean())):.3e}, mean {px.mean():.6f} (ref {ref.mean():.6f}), nan {int(np.isnan(px).sum())}")
+    else:
+        np.save(ref_path, px)
 print(f"{os.environ.get('TRT_B200_JIT_DEFS', '')} {which}: {r.kernel_name()}: trace {best:.2f} ms, {st.samples_traced / best / 1e3:.1f} Msamples/s, {st.bounces / st.samples_traced:.2f} bounces/sample; first frame incl. upload/compile {first * 1e3:.0f} ms", flush=True)
