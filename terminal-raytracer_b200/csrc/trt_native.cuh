@@ -37,26 +37,17 @@ namespace trt {
 #ifndef TRT_NV_CTAS_PER_SM
 #define TRT_NV_CTAS_PER_SM 8
 #endif
-// guarded variants (A/B through TRT_B200_JIT_DEFS / the Makefile's VARIANTS):
-// TRT_V_EXTRA_NOWAIT: an adaptive extra sample only adds to the pixel's sum (shader.wgsl:596), so it is finished
-//   without waiting for its queued light samples; they land in the lane's late sum until the pixel's last sample,
-//   which waits for all of them (the sum of squares of the base samples still needs every sample complete);
-// TRT_NV_WAIT_W: weight of a waiting lane in the flush rule of the queue
-#ifndef TRT_V_EXTRA_NOWAIT
-#define TRT_V_EXTRA_NOWAIT 1
-#endif
-#ifndef TRT_NV_WAIT_W
-#define TRT_NV_WAIT_W 1
-#endif
-// TRT_X_NOWAIT_ALL (measurement only, never shipped on): every sample but a pixel's last is finished without
-//   waiting -- the upper bound of what parking can gain (the variance is then wrong);
+// Tuning switches (A/B through TRT_B200_JIT_DEFS / the Makefile's VARIANTS; measured in profiles/r1_ab_variants_v6.txt):
+// TRT_NV_WAIT_W: weight of a waiting lane in the flush rule of the queue;
 // TRT_NV_SLOTS (power of two): a BASE sample whose light samples are still queued is parked in shared memory
 //   (its radiance so far, and the number of entries the lane had posted when it ended) and the lane starts the next
 //   sample; queue entries carry the sample's slot, so every parked sample has its own late sum.  Parked samples are
 //   closed in sample order as soon as their entries are resolved: the sums of :549-551 see the same values in the
 //   same order as without parking.  1 = no parking.
-#ifndef TRT_X_NOWAIT_ALL
-#define TRT_X_NOWAIT_ALL 0
+// An adaptive EXTRA sample only adds to the pixel's sum (shader.wgsl:596): it is finished without waiting, its light
+// samples land in slot 0's late sum until the pixel's last sample, which waits for all of them.
+#ifndef TRT_NV_WAIT_W
+#define TRT_NV_WAIT_W 1
 #endif
 #ifndef TRT_NV_SLOTS
 #define TRT_NV_SLOTS 4
@@ -68,6 +59,15 @@ enum { NM_ACTIVE = 0, NM_WAIT = 1, NM_NEED_PIXEL = 2, NM_DONE = 3 };
 // queue entry, 11 words: hit point, unit normal (facing the ray), colour x attenuation, random state before
 // the light loop (advanced light by light while the entry is being resolved), meta = owner thread | mask << 8
 enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ_META, DQ_FIELDS };
+
+// Explicit shared-space accesses of the per-lane record (32-bit shared addresses: base + immediate, no generic
+// pointer kept in a register across the loop); "memory": ordered against the warp barriers around them.
+__device__ __forceinline__ float lds_f(unsigned a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ unsigned lds_u(unsigned a) { unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ void sts_f(unsigned a, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void sts_u(unsigned a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void red_f(unsigned a, float v) { asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
+__device__ __forceinline__ void red_u(unsigned a, unsigned v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 
 // The sample of light k for a queued hit (shader.wgsl:350-429): sample point from the two draws (:352-389), the
 // two cosines (:403-404) and, when both are positive, the shadow ray (:394-399) and the clamped contribution
@@ -122,13 +122,11 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     // an entry is resolved whole, at its last light).  The two-stage queue of SrcTiled resolves a light sample that
     // is not needed on the spot, ahead of older samples still in the ray FIFO: no parking there (one slot).
     constexpr unsigned kSlots = SRC::kTiled ? 1u : (unsigned)TRT_NV_SLOTS;
-    __shared__ float s_late[kSlots][3][TRT_NV_THREADS];
-#if TRT_NV_SLOTS > 1
-    __shared__ float s_park[kSlots][3][TRT_NV_THREADS];          // radiance of a parked sample before its late sum
-    __shared__ unsigned s_mark[kSlots][TRT_NV_THREADS];          // entries the lane had posted when that sample ended
-#endif
-    __shared__ unsigned s_res[TRT_NV_THREADS];
-    __shared__ uint32_t s_b0[TRT_NV_THREADS];    // the lane's bounce counter when its pixel began (-> fp.cost)
+    // per-lane record (words): late sum [slot][3], parked radiance [slot][3], entries posted when the parked sample
+    // ended [slot], entries resolved so far, the lane's bounce counter when its pixel began (-> fp.cost); odd stride
+    constexpr unsigned kLate = 0u, kPark = 3u * kSlots, kMark = 6u * kSlots, kRes = 7u * kSlots, kB0 = kRes + 1u;
+    constexpr unsigned kRec = (kB0 + 1u) | 1u;
+    __shared__ float s_lane[TRT_NV_THREADS * kRec];
     __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
     // SrcTiled: second FIFO, of ready shadow rays (origin, direction, contribution, t_max in DQ_RNG, owner in DQ_META)
     __shared__ float s_rays[SRC::kTiled ? TRT_NV_THREADS / 32 : 1][DQ_FIELDS][SRC::kTiled ? TRT_NV_RING : 1];
@@ -136,15 +134,10 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     const unsigned lt_mask = (1u << lane) - 1u;
     float (*ring)[TRT_NV_RING] = s_ring[tid >> 5];
     float (*rays)[SRC::kTiled ? TRT_NV_RING : 1] = s_rays[SRC::kTiled ? tid >> 5 : 0];
-    // the late sum of slot s, component c, of this lane: late[(3 * s + c) * TRT_NV_THREADS]
-    volatile float *late = &s_late[0][0][tid];
-#if TRT_NV_SLOTS <= 1
-    volatile float *late_x = late, *late_y = late + TRT_NV_THREADS, *late_z = late + 2 * TRT_NV_THREADS;
-#endif
-    volatile unsigned *res = &s_res[tid];
+    const unsigned lane_base = (unsigned)__cvta_generic_to_shared(s_lane);
+#define TRT_REC(thread, word) (lane_base + 4u * ((thread) * kRec + (word)))
 #pragma unroll
-    for (int i = 0; i < 3 * (int)kSlots; i++) late[i * TRT_NV_THREADS] = 0.0f;
-    *res = 0u;
+    for (unsigned i = 0; i < kRec; i++) sts_u(TRT_REC(tid, i), 0u);
     __syncwarp();
 
     uint32_t head = 0, tail = 0;                 // FIFO counters, identical in every lane of the warp
@@ -156,9 +149,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     uint32_t pend = 0;                           // entries this lane has posted so far
     int mode = NM_NEED_PIXEL;
     uint32_t xy = 0, rng = 0, si = 0, target = 0, depth = 0, fslot = 0;
-#if TRT_NV_SLOTS > 1
     uint32_t fin = 0;                            // samples of the pixel closed so far; fin .. si - 1 are parked
-#endif
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
     bool extra_phase = false;
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
@@ -183,28 +174,16 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         // ---- finish the sample of a lane whose path has ended and whose queue entries are all resolved ------
         // (shader.wgsl:548-551, :555-565, :596-621)
         bool new_ray = false;
-#if TRT_NV_SLOTS <= 1
-        const bool early = (TRT_X_NOWAIT_ALL || (TRT_V_EXTRA_NOWAIT && extra_phase)) && si + 1u != target;
-        if (mode == NM_WAIT && (early || *res == pend)) {
-            if (!early) {
-                acc = V::add(acc, f3(*late_x, *late_y, *late_z));
-                *late_x = 0.0f; *late_y = 0.0f; *late_z = 0.0f;
-            }
-            tr.n_samples++;
-            pixel_color = V::add(pixel_color, acc);
-            if (!extra_phase) sq_sum = V::add(sq_sum, V::mulv(acc, acc));
-#else
-        bool retire = false;
+        bool retire = false, closed = false;
         if (mode == NM_WAIT) {
-            const unsigned r = *res;
+            const unsigned r = lds_u(TRT_REC(tid, kRes));
             // parked samples whose entries have all been resolved, oldest first
-            while (fin != si) {
+            while (kSlots > 1u && fin != si) {
                 const unsigned ps = fin & (kSlots - 1u);
-                if ((int)(r - s_mark[ps][tid]) < 0) break;
-                volatile float *pl = late + 3u * ps * TRT_NV_THREADS;
-                const float3 a = f3(s_park[ps][0][tid] + pl[0], s_park[ps][1][tid] + pl[TRT_NV_THREADS],
-                                    s_park[ps][2][tid] + pl[2 * TRT_NV_THREADS]);
-                pl[0] = 0.0f; pl[TRT_NV_THREADS] = 0.0f; pl[2 * TRT_NV_THREADS] = 0.0f;
+                if ((int)(r - lds_u(TRT_REC(tid, kMark + ps))) < 0) break;
+                const unsigned al = TRT_REC(tid, kLate + 3u * ps), ap = TRT_REC(tid, kPark + 3u * ps);
+                const float3 a = f3(lds_f(ap) + lds_f(al), lds_f(ap + 4u) + lds_f(al + 4u), lds_f(ap + 8u) + lds_f(al + 8u));
+                sts_f(al, 0.0f); sts_f(al + 4u, 0.0f); sts_f(al + 8u, 0.0f);
                 pixel_color = V::add(pixel_color, a);
                 sq_sum = V::add(sq_sum, V::mulv(a, a));
                 fin++;
@@ -215,27 +194,25 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             const unsigned cs = extra_phase ? 0u : si & (kSlots - 1u);
             const bool last = si + 1u == target;
             if (extra_phase && !last) {
-                fin++;
-                retire = true;
+                retire = closed = true;
             } else if (fin == si && r == pend) {
-                volatile float *pl = late + 3u * cs * TRT_NV_THREADS;
-                acc = V::add(acc, f3(pl[0], pl[TRT_NV_THREADS], pl[2 * TRT_NV_THREADS]));
-                pl[0] = 0.0f; pl[TRT_NV_THREADS] = 0.0f; pl[2 * TRT_NV_THREADS] = 0.0f;
-                fin++;
-                retire = true;
+                const unsigned al = TRT_REC(tid, kLate + 3u * cs);
+                acc = V::add(acc, f3(lds_f(al), lds_f(al + 4u), lds_f(al + 8u)));
+                sts_f(al, 0.0f); sts_f(al + 4u, 0.0f); sts_f(al + 8u, 0.0f);
+                retire = closed = true;
             } else if (!last && si + 1u - fin < kSlots) {
-                s_park[cs][0][tid] = acc.x; s_park[cs][1][tid] = acc.y; s_park[cs][2][tid] = acc.z;
-                s_mark[cs][tid] = pend;                        // its value joins the sums when it is closed
+                const unsigned ap = TRT_REC(tid, kPark + 3u * cs);
+                sts_f(ap, acc.x); sts_f(ap + 4u, acc.y); sts_f(ap + 8u, acc.z);
+                sts_u(TRT_REC(tid, kMark + cs), pend);         // its value joins the sums when it is closed
                 retire = true;
             }
         }
         if (retire) {
-            tr.n_samples++;
-            if (fin == si + 1u) {                              // closed (not parked)
+            if (closed) {
+                fin++;
                 pixel_color = V::add(pixel_color, acc);
                 if (!extra_phase) sq_sum = V::add(sq_sum, V::mulv(acc, acc));
             }
-#endif
             si++;
             bool finished = false;
             float variance_value = 0.0f;
@@ -256,7 +233,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             if (finished) {
                 if (extra_phase) pixel_color = V::divs(V::scale(pixel_color, fp.spp_f), __uint2float_rn(target));
                 tr.finish_pixel(xy & 0xffffu, xy >> 16, pixel_color, variance_value, fslot);
-                if (fp.cost) fp.cost[(size_t)(xy >> 16) * fp.width + (xy & 0xffffu)] = tr.n_bounces - s_b0[tid];
+                tr.n_samples += target;                        // the samples this pixel traced
+                if (fp.cost) fp.cost[(size_t)(xy >> 16) * fp.width + (xy & 0xffffu)] = tr.n_bounces - lds_u(TRT_REC(tid, kB0));
 #if TRT_TAIL_DIAG >= 2
                 if (saw_dry) {                                 // the last 250 pixels to finish: who, how long, from when to when
                     unsigned long long t;
@@ -299,13 +277,11 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     pixel_color = f3(0, 0, 0);
                     sq_sum = f3(0, 0, 0);
                     si = 0;
-#if TRT_NV_SLOTS > 1
                     fin = 0;
-#endif
                     target = fp.base_samples;
                     extra_phase = false;
                     new_ray = true;
-                    s_b0[tid] = tr.n_bounces;
+                    sts_u(TRT_REC(tid, kB0), tr.n_bounces);
 #if TRT_TAIL_DIAG >= 2
                     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_pix));
 #endif
@@ -381,7 +357,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     const float3 C = f3(ring[DQ_CX][ee], ring[DQ_CY][ee], ring[DQ_CZ][ee]);
                     needed = nee_sample<SHAPE>(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                         __uint2float_rn(erng) * 2.3283064365386963e-10f, so, sd, st, scn);
-                    if (!needed) atomicAdd(&s_res[owner & 0xffu], 1u);
+                    if (!needed) red_u(TRT_REC(owner & 0xffu, kRes), 1u);
                 }
                 const unsigned mn = __ballot_sync(0xffffffffu, needed);
                 if (needed) {
@@ -475,13 +451,12 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         if (spass) {                                              // shader.wgsl:402-431 for the queued samples
             if (qvalid) {
                 if (t_hit < 0.0f && qneed) {
-                    atomicAdd(&s_late[qslot][0][qowner], qc.x);
-                    atomicAdd(&s_late[qslot][1][qowner], qc.y);
-                    atomicAdd(&s_late[qslot][2][qowner], qc.z);
+                    const unsigned al = TRT_REC(qowner, kLate + 3u * qslot);
+                    red_f(al, qc.x); red_f(al + 4u, qc.y); red_f(al + 8u, qc.z);
                 }
-                if (SRC::kTiled) atomicAdd(&s_res[qowner], 1u);
+                if (SRC::kTiled) red_u(TRT_REC(qowner, kRes), 1u);
                 else if (qrest) ring[DQ_RNG][qe] = __uint_as_float(qrng);
-                else atomicAdd(&s_res[qowner], 1u);
+                else red_u(TRT_REC(qowner, kRes), 1u);
             }
             if (SRC::kTiled) {
                 rhead += qn;
@@ -585,6 +560,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     }
 #endif
     tr.flush_stats();
+#undef TRT_REC
 }
 
 template <class SRC, class SHAPE>
