@@ -124,7 +124,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     constexpr unsigned kSlots = SRC::kTiled ? 1u : (unsigned)TRT_NV_SLOTS;
     // per-lane record (words): late sum [slot][3], parked radiance [slot][3], entries posted when the parked sample
     // ended [slot], entries resolved so far, the lane's bounce counter when its pixel began (-> fp.cost); odd stride
-    constexpr unsigned kLate = 0u, kPark = 3u * kSlots, kMark = 6u * kSlots, kRes = 7u * kSlots, kB0 = kRes + 1u;
+    // (one slot: nothing is ever parked, the record is late sum, resolved count, bounce mark = 5 words)
+    constexpr unsigned kLate = 0u, kPark = kSlots > 1u ? 3u * kSlots : 0u, kMark = kSlots > 1u ? 6u * kSlots : 0u;
+    constexpr unsigned kRes = kSlots > 1u ? 7u * kSlots : 3u, kB0 = kRes + 1u;
     constexpr unsigned kRec = (kB0 + 1u) | 1u;
     __shared__ float s_lane[TRT_NV_THREADS * kRec];
     __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
@@ -200,7 +202,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 acc = V::add(acc, f3(lds_f(al), lds_f(al + 4u), lds_f(al + 8u)));
                 sts_f(al, 0.0f); sts_f(al + 4u, 0.0f); sts_f(al + 8u, 0.0f);
                 retire = closed = true;
-            } else if (!last && si + 1u - fin < kSlots) {
+            } else if (kSlots > 1u && !last && si + 1u - fin < kSlots) {
                 const unsigned ap = TRT_REC(tid, kPark + 3u * cs);
                 sts_f(ap, acc.x); sts_f(ap + 4u, acc.y); sts_f(ap + 8u, acc.z);
                 sts_u(TRT_REC(tid, kMark + cs), pend);         // its value joins the sums when it is closed
