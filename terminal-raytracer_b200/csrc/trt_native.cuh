@@ -21,10 +21,12 @@
 //     entry and, light by light (warp-uniform index: no divergence on the light type), re-derives the two
 //     draws, evaluates the light sample (:352-389), the cosines and the clamped contribution (:403-429) and
 //     scans its shadow ray (:394-400); an unoccluded contribution is added to the owner's "late" sum;
-//   * a sample is finished (:548-551) only when every entry it posted is resolved; a lane whose path ends
-//     earlier waits (waiting lanes make the queue flush sooner).
-// Per pixel the order of random draws, of samples and of bounces is the shader's; only the order in
-// which a sample's light contributions are summed differs (rounding-level, inside conv 2's tolerance).
+//   * a base sample is closed (:548-551) only when every entry it posted is resolved, but the lane does not wait
+//     for that: the sample is parked (TRT_NV_SLOTS below) and the next one starts; an adaptive extra sample is
+//     finished at once and its light samples join the pixel's sum (:596) any time before the pixel ends.  Only the
+//     last sample of a phase waits (waiting lanes make the queue flush sooner).
+// Per pixel the order of random draws, of samples and of bounces is the shader's; only the order in which light
+// contributions are summed differs (rounding-level, inside conv 2's tolerance).
 // There is no limit on the number of lights beyond the 16-bit mask (TRT_NV_MAX_LIGHTS).
 #pragma once
 #include "trt_trace.cuh"
