@@ -165,6 +165,11 @@ __device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool
 #ifndef TRT_V_CAMFOLD
 #define TRT_V_CAMFOLD 1
 #endif
+// TRT_V_SHIFT_T (candidate, not measured yet): plane / triangle accept tests of the unrolled small-scene scan on
+// t' = t - t_min compared as unsigned integers (one compare instead of two and a predicate merge)
+#ifndef TRT_V_SHIFT_T
+#define TRT_V_SHIFT_T 0
+#endif
 
 template <int CONV, bool COUNT, class SRC>
 struct Tracer {
@@ -537,12 +542,22 @@ struct Tracer {
                 if (t > 0.0f) { closest = t; best = j; }
             }
         }
+#if TRT_V_SHIFT_T
+        // From here on the bound is kept as the bits of closest' = closest - t_min: for t' >= +0 the float order is the
+        // unsigned integer order, and a negative or NaN t' has its sign / exponent bits above every valid bound, so
+        // `t_min <= t < closest` is ONE unsigned compare.  (conv 2: t' is rounded once more than t; a triangle at
+        // exactly t_min is accepted, :214 has `>`.)  A bound at or below t_min accepts nothing.
+        unsigned cb = closest > t_min ? __float_as_uint(closest - t_min) : 0u;
+#endif
         if (n_pl > 0) {
             // a dead axis (|d| < 1e-4, :180) gets a NaN reciprocal: its t is NaN and fails both accept compares
             const float nan = __int_as_float(0x7fc00000);
             const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
                                   fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
-            const float3 roi = V::mulv(ro, inv);
+            float3 roi = V::mulv(ro, inv);
+#if TRT_V_SHIFT_T
+            roi = f3(roi.x + t_min, roi.y + t_min, roi.z + t_min);         // axis-aligned planes yield t' directly
+#endif
 #pragma unroll
             for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NP : TRT_STATIC_P); j++) {
                 if (j < n_pl) {
@@ -556,8 +571,15 @@ struct Tracer {
                         const float3 n = xyz(c_small.pl_n[j]);
                         const float denom = V::dot(n, rd);
                         t = V::dot(V::sub(xyz(p), ro), n) * (fabsf(denom) >= 0.0001f ? rcp_native(denom) : nan);
+#if TRT_V_SHIFT_T
+                        t -= t_min;
+#endif
                     }
+#if TRT_V_SHIFT_T
+                    if (__float_as_uint(t) < cb) { cb = __float_as_uint(t); best = n_sph + j; }
+#else
                     if (t >= t_min && t < closest) { closest = t; best = n_sph + j; }
+#endif
                 }
             }
         }
@@ -583,12 +605,20 @@ struct Tracer {
                         const float v = f * dotz(rd, q, qx0, qy0, qz0);
                         if (!(v < 0.0f || u + v > 1.0f)) {
                             const float t = f * dotz(e2, q, e2x0 || qx0, e2y0 || qy0, e2z0 || qz0);
+#if TRT_V_SHIFT_T
+                            const unsigned tb = __float_as_uint(t - t_min);
+                            if (tb < cb) { cb = tb; best = n_sph + n_pl + j; }
+#else
                             if (t > t_min && t < closest) { closest = t; best = n_sph + n_pl + j; }
+#endif
                         }
                     }
                 }
             }
         }
+#if TRT_V_SHIFT_T
+        closest = __uint_as_float(cb) + t_min;
+#endif
         return best >= 0 ? closest : -1.0f;
     }
 
