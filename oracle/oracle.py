@@ -1,5 +1,6 @@
 """
-oracle.py -- Python face of the CPU ORACLE (test infrastructure only; PARITY UNPINNED).
+oracle.py -- Python face of the CPU ORACLE (test infrastructure only; conv 0 is pinned bit for bit to
+oracle/_ref, the reference's shader.wgsl transliterated and compiled here -- see trt_oracle.h).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
 this module.  It holds
@@ -21,6 +22,11 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "liboracle.so")
+FAST_LIB_PATH = os.path.join(HERE, "liboracle_fast.so")     # -O3 -march=native: the timed cpu_baseline leg
+REF_DIR = os.path.join(HERE, "_ref")
+REF_LIB_PATH = os.path.join(REF_DIR, "libref.so")           # the reference's shader.wgsl, transliterated + compiled
+REF_FMA_LIB_PATH = os.path.join(REF_DIR, "libref_fma.so")   # the same text with FMA contraction allowed
+REF_SOURCE = "/root/reference/src/shader.wgsl"
 
 # ---- wire formats ------------------------------------------------------------------------------
 VEC3 = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("pad", "<f4")])
@@ -58,7 +64,8 @@ _lib = None
 def build(force: bool = False) -> str:
     """Compile liboracle.so with oracle/Makefile (gcc only; no reference sources involved)."""
     srcs = [os.path.join(HERE, f) for f in
-            ("trt_oracle.c", "trt_oracle_quant.c", "trt_oracle_core.inc", "trt_oracle.h", "Makefile")]
+            ("trt_oracle.c", "trt_oracle_quant.c", "trt_oracle_core.inc", "trt_oracle.h", "trt_sincos_pinned.h",
+             "Makefile")]
     stale = force or not os.path.exists(LIB_PATH) or any(
         os.path.getmtime(s) > os.path.getmtime(LIB_PATH) for s in srcs)
     if stale:
@@ -105,6 +112,118 @@ def lib() -> C.CDLL:
         L.oracle_max_threads.restype = C.c_int
         _lib = L
     return _lib
+
+
+_fast = None
+
+
+def fast_lib() -> C.CDLL:
+    """liboracle_fast.so (-O3 -march=native -ffp-contract=off): same sources, same bits (tested), used by the
+    TIMED cpu_baseline / --impl reference legs only."""
+    global _fast
+    if _fast is None:
+        srcs = [os.path.join(HERE, f) for f in ("trt_oracle.c", "trt_oracle_quant.c", "trt_oracle_core.inc",
+                                                "trt_oracle.h", "trt_sincos_pinned.h", "Makefile")]
+        if not os.path.exists(FAST_LIB_PATH) or any(os.path.getmtime(x) > os.path.getmtime(FAST_LIB_PATH)
+                                                     for x in srcs):
+            try:
+                subprocess.run(["make", "-C", HERE, "-s", "liboracle_fast.so"], check=True,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            except Exception:
+                if not os.path.exists(FAST_LIB_PATH):
+                    raise
+        L = C.CDLL(FAST_LIB_PATH)
+        L.oracle_render.restype = C.c_int
+        L.oracle_render.argtypes = lib().oracle_render.argtypes
+        _fast = L
+    return _fast
+
+
+# ---- oracle/_ref: the reference's own shader text, compiled here -------------------------------------
+_ref = {}
+
+
+def ref_build() -> bool:
+    """(Re)build oracle/_ref/*.so from /root/reference/src/shader.wgsl where that file exists (this container).
+    On the GPU box the prebuilt files travel with the snapshot and nothing is rebuilt."""
+    if not os.path.exists(REF_SOURCE):
+        return os.path.exists(REF_LIB_PATH)
+    subprocess.run(["make", "-C", HERE, "-s", "ref"], check=True, stdout=subprocess.DEVNULL,
+                   stderr=subprocess.DEVNULL)
+    return True
+
+
+def ref_available() -> bool:
+    try:
+        return ref_build() and os.path.exists(REF_LIB_PATH)
+    except Exception:
+        return os.path.exists(REF_LIB_PATH)
+
+
+def ref_lib(fma: bool = False) -> C.CDLL:
+    path = REF_FMA_LIB_PATH if fma else REF_LIB_PATH
+    if path not in _ref:
+        if not ref_available() or not os.path.exists(path):
+            raise FileNotFoundError(f"{path}: the transliterated reference shader is not built "
+                                    f"(needs {REF_SOURCE} at build time)")
+        L = C.CDLL(path)
+        f32p, u32p = C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+        L.ref_pcg_hash.restype = C.c_uint32
+        L.ref_pcg_hash.argtypes = [C.c_uint32]
+        L.ref_rng_stream.restype = None
+        L.ref_rng_stream.argtypes = [C.c_uint32] * 6 + [u32p, f32p]
+        L.ref_hit.restype = C.c_float
+        L.ref_hit.argtypes = [C.c_void_p, f32p, f32p, C.c_float, C.c_float]
+        L.ref_render.restype = C.c_int
+        L.ref_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p,
+                                 C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_max_threads.restype = C.c_int
+        _ref[path] = L
+    return _ref[path]
+
+
+def ref_render(prims: np.ndarray, u: np.ndarray, accumulation: np.ndarray | None = None, math_mode=0, threads=0,
+               rows=None, idx=None, fma=False):
+    """One dispatch of the transliterated reference shader; same arguments and result layout as render()."""
+    w, h = int(u["width"]), int(u["height"])
+    prims = np.ascontiguousarray(prims)
+    assert prims.dtype == PRIM and len(prims) >= int(u["primitive_count"])
+    ub = np.ascontiguousarray(u.reshape(1))
+    n = len(idx) if idx is not None else w * h
+    if accumulation is None:
+        accumulation = np.zeros((n, 4), np.float32)
+    else:
+        accumulation = np.ascontiguousarray(accumulation, np.float32).reshape(n, 4).copy()
+    pixels = np.zeros((n, 4), np.float32)
+    var = np.zeros(n, VARIANCE)
+    y0, y1 = rows if rows is not None else (0, h)
+    if idx is not None:
+        idx = np.ascontiguousarray(idx, np.uint32)
+    rc = ref_lib(fma).ref_render(prims.ctypes.data, ub.ctypes.data, math_mode, threads, y0, y1,
+                                 idx.ctypes.data if idx is not None else None, n if idx is not None else 0,
+                                 accumulation.ctypes.data, pixels.ctypes.data, var.ctypes.data)
+    if rc != 0:
+        raise ValueError("ref_render: bad arguments")
+    return {"accumulation": accumulation, "pixels": pixels, "variance": var}
+
+
+def ref_pcg_hash(v: int) -> int:
+    return int(ref_lib().ref_pcg_hash(C.c_uint32(v & 0xFFFFFFFF)))
+
+
+def ref_rng_stream(x, y, w, seed, frame, n):
+    st = np.zeros(n, np.uint32)
+    va = np.zeros(n, np.float32)
+    ref_lib().ref_rng_stream(x, y, w, seed & 0xFFFFFFFF, frame, n,
+                             st.ctypes.data_as(C.POINTER(C.c_uint32)), va.ctypes.data_as(C.POINTER(C.c_float)))
+    return st, va
+
+
+def ref_hit(prim: np.ndarray, o, d, tmin, tmax):
+    """hit_sphere / hit_plane / hit_triangle of the transliterated shader on one 180-byte primitive record."""
+    rec = np.ascontiguousarray(prim.reshape(1))
+    (_, po), (_, pd) = _f3(o), _f3(d)
+    return np.float32(ref_lib().ref_hit(rec.ctypes.data, po, pd, tmin, tmax))
 
 
 def _f3(v):
@@ -251,7 +370,7 @@ def make_uniforms(scene: dict, n_prims: int, seed: int, frame_number: int, camer
 
 # ---- render / quantise -----------------------------------------------------------------------------
 def render(prims: np.ndarray, u: np.ndarray, accumulation: np.ndarray | None = None, conv=0, math_mode=0,
-           threads=0, rows=None, idx=None, want_counters=False):
+           threads=0, rows=None, idx=None, want_counters=False, fast=False):
     """One frame of shader.wgsl main().  Returns dict(accumulation, pixels, variance[, counters])."""
     w, h = int(u["width"]), int(u["height"])
     prims = np.ascontiguousarray(prims)
@@ -269,7 +388,7 @@ def render(prims: np.ndarray, u: np.ndarray, accumulation: np.ndarray | None = N
     traced = C.c_uint64(0)
     if idx is not None:
         idx = np.ascontiguousarray(idx, np.uint32)
-    rc = lib().oracle_render(prims.ctypes.data, ub.ctypes.data, conv, math_mode, threads, y0, y1,
+    rc = (fast_lib() if fast else lib()).oracle_render(prims.ctypes.data, ub.ctypes.data, conv, math_mode, threads, y0, y1,
                              idx.ctypes.data if idx is not None else None, n if idx is not None else 0,
                              accumulation.ctypes.data, pixels.ctypes.data, var.ctypes.data,
                              cnt.ctypes.data if cnt is not None else None, C.byref(traced))

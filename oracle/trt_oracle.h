@@ -5,11 +5,17 @@
  * bench.py's cpu_baseline / --impl reference legs may load it.  The product (libtrt_b200.so)
  * never links, loads or calls anything in oracle/.
  *
- * PARITY UNPINNED: the reference (Gooey321/Terminal-Raytracer) has no tests, no golden vectors and
- * cannot be compiled or run here (no Rust toolchain, wgpu needs a graphics adapter).  This oracle is
- * a scalar f32 restatement of the reference's WGSL compute shader (src/shader.wgsl) and of its Rust
- * quantiser (src/lib.rs:503-529), pinned only by the source text and by the known-answer values
- * derived from it by hand (tests/test_oracle_kat.py).
+ * PARITY PIN: the reference (Gooey321/Terminal-Raytracer) has no tests and no golden vectors, and it cannot be
+ * run through wgpu here (no Rust toolchain, no graphics adapter).  Its path tracer, however, is one WGSL file of
+ * plain scalar code, and oracle/_ref/libref.so is that file compiled here: oracle/wgsl2c.py transliterates
+ * /root/reference/src/shader.wgsl to C at build time (one statement per statement; the generated text never
+ * enters the repo) and oracle/Makefile compiles it with -ffp-contract=off.  tests/test_oracle_ref.py shows this
+ * hand-written restatement (conv 0) returns the SAME BITS as that build -- pixels, accumulation, variance -- on
+ * the three shipped scenes, spp 1..128, depth 0..32, frames 0..3 and a reduced C4 scene, and the conv 0 golden
+ * fixtures (tests/golden/frames.*) are outputs of that build.  What remains a hand restatement pinned only by the
+ * source text: the Rust quantiser (src/lib.rs:503-529, trt_oracle_quant.c) and the host data path (oracle.py);
+ * the implementation-defined arithmetic of WGSL (sqrt / sin / cos / tan / division accuracy, contraction) is
+ * fixed by the conventions below for both builds alike.
  *
  * Arithmetic conventions (the reference leaves them to naga + the GPU driver, so they are chosen
  * here and stated; see DESIGN.md "Arithmetic conventions"):

@@ -1,6 +1,6 @@
 /*
  * trt_oracle_quant.c -- CPU ORACLE for the terminal quantiser (test infrastructure only; PARITY
- * UNPINNED, see trt_oracle.h).  Restates /root/reference/src/lib.rs:503-532: one row of ANSI text
+ * pinned only by the source text: the quantiser is Rust and stays a hand restatement, see trt_oracle.h).  Restates /root/reference/src/lib.rs:503-532: one row of ANSI text
  * per image row, rows concatenated in order.  f32 arithmetic, glibc powf/sqrtf (= Rust f32::powf /
  * f32::sqrt on Linux), Rust `as u8` / `as usize` cast semantics (truncate, saturate, NaN -> 0),
  * Rust f32::clamp (NaN stays NaN) and f32::min (NaN.min(a) == a).
