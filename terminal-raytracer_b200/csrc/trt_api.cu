@@ -470,6 +470,7 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     fp.seed = u->seed; fp.frame_number = u->frame_number;
     fp.base_samples = u->samples_per_pixel / 4u < 4u ? 4u : u->samples_per_pixel / 4u;     // shader.wgsl:513
     fp.n_local_pixels = (uint32_t)(ctx->rows.size() * (size_t)u->width);
+    fp.all_ones = 0xffffffffu;
     fp.char_aspect = u->char_aspect_ratio;
     fp.half_h = tanf(u->fov_rad / 2.0f);                 // shader.wgsl:522, frame-uniform: evaluated once (glibc)
     fp.half_w = u->aspect_ratio * fp.half_h;             // shader.wgsl:523

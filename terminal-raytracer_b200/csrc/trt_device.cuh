@@ -49,7 +49,8 @@ struct SceneView {
 struct FrameParams {
     uint32_t width, height, spp, max_depth;
     uint32_t seed, frame_number, base_samples, n_local_pixels;
-    float inv_unused, char_aspect, half_h, half_w;      // half_h = tan(fov/2) (host, glibc), half_w = aspect*half_h
+    uint32_t all_ones;                                  // 0xffffffff, as a value the compiler cannot fold (TRT_V_KEY: a mask kept in a register)
+    float char_aspect, half_h, half_w;                  // half_h = tan(fov/2) (host, glibc), half_w = aspect*half_h
     float wm1, hm1;                                     // f32(width-1), f32(height-1)
     float spp_f, base_f;
     // conv 2 camera ray with the frame-uniform factors folded on the host (TRT_V_CAMFOLD): view-plane coordinates

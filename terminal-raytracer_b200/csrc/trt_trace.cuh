@@ -170,6 +170,20 @@ __device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool
 #ifndef TRT_V_SHIFT_T
 #define TRT_V_SHIFT_T 0
 #endif
+// TRT_V_KEY: the bound of the unrolled small-scene scan as ONE ordered key -- the bits of t' = t - t_min with the low
+// index bits replaced by the primitive index.  For t' >= +0 the float order is the unsigned order, a negative or NaN t'
+// sorts above every valid bound, so `t_min <= t < closest, remember who` is FFMA + LOP3 + (half a) VIMNMX3.U32 per plane
+// (as written: FFMA + 2 FSETP + PLOP3 + FSEL + SEL).  Equal keys keep the lower index = the first primitive in scan
+// order (shader.wgsl:279).  Cost: t is known to 2^-19 relative (4 index bits) instead of 2^-24 -- conv 2 only,
+// inside its tolerance (tests/test_gpu_native.py).  B200, A/B frame: 39.94 -> 38.65 ms (profiles/r2_ab_variants.txt).
+#ifndef TRT_V_KEY
+#define TRT_V_KEY 1
+#endif
+// TRT_V_NO_RENORM: cosine_hemisphere_unit returns u*x + v*y + w*z without the final normalize (:334): (u, v, w) is
+// orthonormal and x^2 + y^2 + z^2 = 1 up to rounding, so the length is 1 +- a few ulp already.  38.65 -> 38.41 ms.
+#ifndef TRT_V_NO_RENORM
+#define TRT_V_NO_RENORM 1
+#endif
 
 template <int CONV, bool COUNT, class SRC>
 struct Tracer {
@@ -542,7 +556,20 @@ struct Tracer {
                 if (t > 0.0f) { closest = t; best = j; }
             }
         }
-#if TRT_V_SHIFT_T
+#if TRT_V_KEY
+        // index field: 4 / 5 / 6 bits by the scene's primitive count (the same rule for a compile-time and a run-time
+        // count, so that a specialised kernel and the run-time-count kernel quantise t alike); all ones = nothing found.
+        // The mask is derived from a kernel parameter (FrameParams::all_ones), a value the compiler cannot fold, so
+        // that it sits in a register and (bits & mask) | index is ONE LOP3 (register, register, immediate).
+        const int n_tot = n_sph + n_pl + n_tri;
+        const int kb = n_tot < 15 ? 4 : n_tot < 31 ? 5 : 6;
+        const unsigned nkm = fp.all_ones << kb;
+        const unsigned KM = (1u << kb) - 1u;                    // a literal when the shape is fixed
+        // A bound at or below t_min accepts nothing: key 0 is below every candidate.
+        const bool open = closest > t_min;
+        unsigned key = open ? ((__float_as_uint(closest - t_min) & nkm) | (best >= 0 ? (unsigned)best : KM)) : 0u;
+#define TRT_KEY_OF(tp, idx) ((__float_as_uint(tp) & nkm) | (unsigned)(idx))
+#elif TRT_V_SHIFT_T
         // From here on the bound is kept as the bits of closest' = closest - t_min: for t' >= +0 the float order is the
         // unsigned integer order, and a negative or NaN t' has its sign / exponent bits above every valid bound, so
         // `t_min <= t < closest` is ONE unsigned compare.  (conv 2: t' is rounded once more than t; a triangle at
@@ -555,7 +582,7 @@ struct Tracer {
             const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
                                   fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
             float3 roi = V::mulv(ro, inv);
-#if TRT_V_SHIFT_T
+#if TRT_V_SHIFT_T || TRT_V_KEY
             roi = f3(roi.x + t_min, roi.y + t_min, roi.z + t_min);         // axis-aligned planes yield t' directly
 #endif
 #pragma unroll
@@ -571,11 +598,13 @@ struct Tracer {
                         const float3 n = xyz(c_small.pl_n[j]);
                         const float denom = V::dot(n, rd);
                         t = V::dot(V::sub(xyz(p), ro), n) * (fabsf(denom) >= 0.0001f ? rcp_native(denom) : nan);
-#if TRT_V_SHIFT_T
+#if TRT_V_SHIFT_T || TRT_V_KEY
                         t -= t_min;
 #endif
                     }
-#if TRT_V_SHIFT_T
+#if TRT_V_KEY
+                    key = min(key, TRT_KEY_OF(t, n_sph + j));
+#elif TRT_V_SHIFT_T
                     if (__float_as_uint(t) < cb) { cb = __float_as_uint(t); best = n_sph + j; }
 #else
                     if (t >= t_min && t < closest) { closest = t; best = n_sph + j; }
@@ -605,7 +634,9 @@ struct Tracer {
                         const float v = f * dotz(rd, q, qx0, qy0, qz0);
                         if (!(v < 0.0f || u + v > 1.0f)) {
                             const float t = f * dotz(e2, q, e2x0 || qx0, e2y0 || qy0, e2z0 || qz0);
-#if TRT_V_SHIFT_T
+#if TRT_V_KEY
+                            key = min(key, TRT_KEY_OF(t - t_min, n_sph + n_pl + j));
+#elif TRT_V_SHIFT_T
                             const unsigned tb = __float_as_uint(t - t_min);
                             if (tb < cb) { cb = tb; best = n_sph + n_pl + j; }
 #else
@@ -616,7 +647,12 @@ struct Tracer {
                 }
             }
         }
-#if TRT_V_SHIFT_T
+#if TRT_V_KEY
+#undef TRT_KEY_OF
+        best = (int)(key & KM);
+        if (!open || best == (int)KM) best = -1;
+        closest = __uint_as_float(key & nkm) + t_min;
+#elif TRT_V_SHIFT_T
         closest = __uint_as_float(cb) + t_min;
 #endif
         return best >= 0 ? closest : -1.0f;
@@ -697,7 +733,11 @@ struct Tracer {
         const float dx = __fmaf_rn(wx, z, __fmaf_rn(-b, t, a * x));
         const float dy = __fmaf_rn(wy, z, nn * y);
         const float dz = __fmaf_rn(w.z, z, __fmaf_rn(-a, t, -(b * x)));
+#if TRT_V_NO_RENORM
+        return f3(use_y ? dx : dy, use_y ? dy : dx, dz);
+#else
         return V::normalize(f3(use_y ? dx : dy, use_y ? dy : dx, dz));
+#endif
     }
 
     // shader.wgsl:338-436.  The loop runs over the precomputed list of emissive spheres/triangles
