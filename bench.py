@@ -13,9 +13,14 @@ fixed as N grows => "scaling": "strong").  --workload c1|c2|c4 select the other 
 `value`  : device-resident (scene + buffers in HBM; trace + accumulate + gather + quantise).
 `e2e`    : the same through trt_render_frame with HOST buffers: uniforms in, byte stream out (pinned).
 `roofline`: trace kernel, FP32: achieved = F_min (algorithmic flops) / CUDA-event time.
-`cpu_baseline`: the oracle (C restatement of the shader; the reference has no CPU tracer) on a bounded
-            strided pixel sample of the same frame, all host threads.
-Only the cpu_baseline / --impl reference legs touch oracle/.
+`roofline_quantise`: the on-device quantiser (pack + scan + emit), algorithmic bytes / its CUDA-event time / HBM peak.
+`cpu_baseline`: the reference's shader compiled for the host (oracle/_ref: shader.wgsl transliterated to C, kind
+            "reference"; the hand-written port, kind "port", where _ref did not travel) on a bounded strided pixel
+            sample of the same frame, all host threads.
+`config.parity`: the named configuration itself checked against that CPU build on a strided pixel subset: the strict
+            (conv 0) frame bit for bit, the benchmarked conv 2 frame by north_star's tolerances.
+The product arm is fed by the product's own host code (Scene.parse / trt_fill_uniforms); only the parity,
+cpu_baseline and --impl reference legs touch oracle/.
 """
 from __future__ import annotations
 
@@ -34,6 +39,7 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as graft  # noqa: E402
 
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # 74.45: SMs x lanes x 2 x max clock
+QUANT_KERNELS = "quant_pack_kernel + quant_scan_kernel + quant_emit_kernel"
 
 
 def workload(name, O, args):
@@ -76,12 +82,39 @@ def sample_indices(w, h, n):
     return np.unique((np.arange(n, dtype=np.float64) * (total / n)).astype(np.uint32))
 
 
+def host_threads():
+    """Threads the CPU legs use: every core this process may run on.  Set explicitly -- torchrun exports
+    OMP_NUM_THREADS=1, which omp_get_max_threads() would obey."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_kind(O):
+    return "reference" if O.ref_available() else "port"
+
+
+def cpu_build(O):
+    if O.ref_available():
+        return ("oracle/_ref/libref.so: /root/reference/src/shader.wgsl transliterated to C (oracle/wgsl2c.py), "
+                "gcc -O2 -ffp-contract=off, OpenMP over pixels")
+    return "oracle/liboracle_fast.so: hand-written port, gcc -O3 -ffp-contract=off, OpenMP over pixels"
+
+
 def cpu_run(O, wl, prims, n_pixels, threads, frame=0):
+    """One timed pass of the CPU build over a strided pixel sample: oracle/_ref (the reference's shader.wgsl
+    transliterated to C) when it is there, else the hand-written port (-O3 build; same bits)."""
     idx = sample_indices(wl["w"], wl["h"], n_pixels)
     u = O.make_uniforms(wl["scene"], len(prims), wl["seed_fn"](frame), 0, width=wl["w"], height=wl["h"], spp=wl["spp"],
                         max_depth=wl["depth"])
+    if O.ref_available():
+        t0 = time.perf_counter()
+        r = O.ref_render(prims, u, idx=idx, threads=threads)
+        dt = time.perf_counter() - t0
+        return O.samples_from_variance(r["variance"], wl["spp"]), dt, len(idx)
     t0 = time.perf_counter()
-    r = O.render(prims, u, idx=idx, threads=threads)
+    r = O.render(prims, u, idx=idx, threads=threads, fast=True)
     dt = time.perf_counter() - t0
     return r["samples_traced"], dt, len(idx)
 
@@ -98,16 +131,17 @@ def cpu_sample_size(O, wl, prims, threads, budget_s):
 
 
 def reference_arm(args):
-    """The reference's own implementation of the path is a WGSL shader behind wgpu (needs a graphics
-    adapter: unavailable on this box) and there is no CPU tracer in it; the reference arm is therefore
-    the oracle's CPU restatement on all host threads, on a bounded strided sample of the same frame."""
+    """The reference's own implementation of the path is a WGSL shader behind wgpu (needs a graphics adapter:
+    unavailable on this box).  The reference arm runs that shader's text compiled for the host (oracle/_ref, built
+    by oracle/wgsl2c.py from /root/reference/src/shader.wgsl; kind "reference") on all host threads, on a bounded
+    strided sample of the same frame; without _ref it falls back to the hand-written port (kind "port")."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     O = graft.load_oracle()
     wl = workload(args.workload, O, args)
     prims = O.flatten_scene(wl["scene"])
-    threads = O.max_threads()
+    threads = host_threads()
     budget = 60.0 / max(1, args.steps + args.warmup)
     n_px = cpu_sample_size(O, wl, prims, threads, min(20.0, max(2.0, budget)))
     for _ in range(args.warmup):
@@ -123,9 +157,66 @@ def reference_arm(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["label"], "l2": "n/a (CPU)"},
-            "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": threads, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": threads, "kind": cpu_kind(O), "sample": sample,
+                             "build": cpu_build(O)},
             "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def parity_block(pkg, O, wl, prims_np, scene, cam, local, conv, n_pixels, native_renderer):
+    """The named configuration itself against the CPU build of the reference's shader, on a strided pixel subset:
+    strict (conv 0) frame bit for bit; the benchmarked convention by north_star's bars (pixels over 1e-4 relative,
+    RMSE against the Monte-Carlo noise floor)."""
+    w, h = wl["w"], wl["h"]
+    idx = sample_indices(w, h, n_pixels)
+    seed = wl["seed_fn"](0)
+    u_np = O.make_uniforms(wl["scene"], len(prims_np), seed, 0, width=w, height=h, spp=wl["spp"], max_depth=wl["depth"])
+    u = scene.uniforms(cam, seed, 0)
+    same_uniforms = bytes(u)[:112] == u_np.tobytes()[:112]          # product host code == oracle restatement
+    use_ref = O.ref_available()
+    t0 = time.perf_counter()
+    ref = O.ref_render(prims_np, u_np, idx=idx) if use_ref else O.render(prims_np, u_np, idx=idx)
+    cpu_s = time.perf_counter() - t0
+    want = ref["pixels"]
+    out = {"checker": "oracle/_ref (shader.wgsl transliterated to C)" if use_ref else "oracle (hand-written port)",
+           "subset_pixels": int(len(idx)), "uniforms_equal_oracle": bool(same_uniforms), "cpu_seconds": round(cpu_s, 2)}
+    # strict build: bits
+    rs = pkg.Renderer(w, h, device=local, conv=0)
+    rs.upload_scene(scene)
+    rs.render_frame(u, pkg.MODE_NONE)
+    got = rs.read_pixels()[idx]
+    var = rs.read_variance()[idx]
+    rs.close()
+    out["strict_bit_mismatches"] = int((got.view(np.uint32) != want.view(np.uint32)).any(axis=1).sum())
+    out["strict_variance_bit_mismatches"] = int((var["variance"].view(np.uint32) != ref["variance"]["variance"].view(np.uint32)).sum())
+    # the benchmarked convention: tolerance
+    if conv != 0:
+        native_renderer.render_frame(u, pkg.MODE_NONE)
+        nat = native_renderer.read_pixels()[idx][:, :3].astype(np.float64)
+        wt = want[:, :3].astype(np.float64)
+        rel = np.abs(nat - wt) / np.maximum(np.abs(wt), 1e-2)
+        out["native_over_1e-4"] = int((rel.max(axis=1) > 1e-4).sum())
+        u2 = O.make_uniforms(wl["scene"], len(prims_np), (seed + 0x9E3779B9) & 0xFFFFFFFF, 0, width=w, height=h, spp=wl["spp"],
+                             max_depth=wl["depth"])
+        other = (O.ref_render(prims_np, u2, idx=idx) if use_ref else O.render(prims_np, u2, idx=idx))["pixels"][:, :3].astype(np.float64)
+        noise = float(np.sqrt(((other - wt) ** 2).mean()))
+        rmse = float(np.sqrt(((nat - wt) ** 2).mean()))
+        out["native_rmse"] = rmse
+        out["noise_rmse_seed_to_seed"] = noise
+        out["native_rmse_vs_noise"] = rmse / noise if noise > 0 else None
+        out["native_mean_rel_diff"] = float(abs(nat.mean() - wt.mean()) / max(wt.mean(), 1e-12))
+        if use_ref:
+            try:
+                fma = O.ref_render(prims_np, u_np, idx=idx, fma=True)["pixels"][:, :3].astype(np.float64)
+                relf = np.abs(fma - wt) / np.maximum(np.abs(wt), 1e-2)
+                out["yardstick_ref_contracted_over_1e-4"] = int((relf.max(axis=1) > 1e-4).sum())
+                out["yardstick_ref_contracted_rmse_vs_noise"] = float(np.sqrt(((fma - wt) ** 2).mean())) / noise if noise > 0 else None
+            except Exception:
+                pass
+        out["note"] = ("strict = conv 0 kernels, compared bit for bit; native = the benchmarked conv 2 kernel by north_star's bars; "
+                       "yardstick = the reference's own text compiled with FMA contraction allowed (another legal rounding of it) "
+                       "against its strict compilation, same pixels")
+    return out
 
 
 class ClockSampler:
@@ -189,19 +280,20 @@ def ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from terminal_raytracer_b200 import multigpu
 
-    O = graft.load_oracle() if rank == 0 else None    # scene data + uniforms restatement; cpu_baseline leg
-    OO = O or graft.load_oracle()                      # (scene constants only on other ranks)
+    OO = graft.load_oracle()                           # module import only: the workload DEFINITIONS (scene data, seeds)
+    O = OO if rank == 0 else None                      # the CPU build itself: parity / cpu_baseline legs on rank 0
     wl = workload(args.workload, OO, args)
-    prims = OO.flatten_scene(wl["scene"])
     w, h, mode = wl["w"], wl["h"], wl["mode"]
+    # the product's own host code: JSON -> SceneConfig -> primitives (trt_scene_parse), camera (trt_camera_default),
+    # per-frame uniforms (trt_fill_uniforms) -- lib.rs:52-154, :118, :417-439
+    scene = pkg.Scene.parse(json.dumps(dict(wl["scene"], width=w, height=h, samples_per_pixel=wl["spp"], max_depth=wl["depth"])))
+    cam = pkg.Camera()
 
     def uniforms(f):
-        u = OO.make_uniforms(wl["scene"], len(prims), wl["seed_fn"](f), f if wl["acc"] else 0, width=w, height=h,
-                             spp=wl["spp"], max_depth=wl["depth"])
-        return pkg.api.uniforms_from_bytes(u.tobytes())
+        return scene.uniforms(cam, wl["seed_fn"](f), f if wl["acc"] else 0)
 
     sr = multigpu.ShardedRenderer(pkg, w, h, rank, world, stripe_rows=args.stripe_rows, device=local, conv=args.conv)
-    sr.upload_scene(prims)
+    sr.upload_scene(scene)
     stream = sr.stream
     frame_bytes = w * h * 16
     small = frame_bytes * 3 < 126 * 2**20
@@ -221,7 +313,7 @@ def ours(args):
     if rank == 0:
         sampler.start()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    trace_ms, combine_ms, samples_local, launches = [], [], 0, 0
+    trace_ms, combine_ms, quant_ms, samples_local, launches = [], [], [], 0, 0
     barrier()
     for k in range(args.steps):
         if flush is not None:
@@ -235,6 +327,7 @@ def ours(args):
         st = sr.step_times()                          # this rank's trace kernel alone / pack + gather / quantise
         trace_ms.append(st[0])
         combine_ms.append(st[1] + st[2])
+        quant_ms.append(st[2])
         launches += t.kernel_launches                 # trace + pack_rows + 3 quantise kernels (rank 0)
         samples_local += sr.r.frame_stats().samples_traced
     barrier()
@@ -309,7 +402,7 @@ def ours(args):
     # ---- roofline of the trace kernel: F_min per sample from the instrumented kernel on a row subset ----
     sub = 1 if w * h * wl["spp"] <= 2_000_000 else max(1, args.count_stride)
     rc = pkg.Renderer(w, h, device=local, conv=args.conv, count_work=True, shard_index=0, shard_count=sub, stripe_rows=1)
-    rc.upload_scene(prims)
+    rc.upload_scene(scene)
     rc.render_frame(uniforms(args.warmup), pkg.MODE_NONE)
     cnt = rc.counters()
     rc.close()
@@ -338,30 +431,58 @@ def ours(args):
                 "flops_basis": f"instrumented kernel on rows y % {sub} == 0 ({n_cnt} samples), DESIGN.md cost table",
                 "trace_ms_per_step": trace_s * 1e3 / args.steps, "per_gpu": True}
 
+    # ---- quantiser (north_star: "achieved HBM GB/s for the accumulate/quantise pass"): K4 over the assembled frame;
+    # algorithmic bytes = 16 B/px read + the exact stream length written -------------------------------------
+    roofline_q = None
+    if world == 1 and mode != pkg.MODE_NONE and quant_ms:
+        stream_len = sr.r.quantise_async(mode, want_len=True)
+        sr.r.sync()
+        hbm, src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+        try:
+            hbm = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+            src = "MEASURED_PEAKS.json hbm_gbs"
+        except (OSError, ValueError, KeyError):
+            pass
+        q_ms = statistics.median(quant_ms)
+        q_bytes = w * h * 16 + stream_len
+        gbs = q_bytes / (q_ms / 1e3) / 1e9 if q_ms > 0 else None
+        roofline_q = {"bound": "hbm", "kernel": QUANT_KERNELS, "achieved": gbs, "peak": hbm, "unit": "GB/s",
+                      "frac": gbs / hbm if gbs else None, "peak_source": src,
+                      "algorithmic_bytes": q_bytes, "ms": q_ms, "stream_bytes": stream_len,
+                      "note": "CUDA events around the quantiser's launches on the context's stream, median of the timed steps"}
+
     # ---- CPU baseline (oracle port, bounded sample) -----------------------------------------------------
     cpu = None
+    prims_np = O.flatten_scene(wl["scene"])
     if world == 1 and not args.no_cpu:
-        threads = O.max_threads()
-        n_px = cpu_sample_size(O, wl, prims, threads, args.cpu_seconds)
-        s, dt, n = cpu_run(O, wl, prims, n_px, threads)
-        cpu = {"value": s / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": "port",
+        threads = host_threads()
+        n_px = cpu_sample_size(O, wl, prims_np, threads, args.cpu_seconds)
+        s, dt, n = cpu_run(O, wl, prims_np, n_px, threads)
+        cpu = {"value": s / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": cpu_kind(O), "build": cpu_build(O),
                "sample": f"{n} of {w * h} pixels on a regular stride ({s} samples, {dt:.1f} s)"}
+
+    # ---- parity of the named configuration itself (strided subset against the CPU build of the reference's shader) ----
+    parity = None
+    if world == 1 and not args.no_parity:
+        parity = parity_block(pkg, O, wl, prims_np, scene, cam, local, args.conv, args.parity_pixels, sr.r)
 
     # ---- the same frame in the strict convention (conv 0: bit-exact against the oracle), for comparison ----
     strict = None
     if world == 1 and args.conv != 0 and not args.no_strict:
         rs = pkg.Renderer(w, h, device=local, conv=0)
-        rs.upload_scene(prims)
+        rs.upload_scene(scene)
         rs.render_frame(uniforms(0), pkg.MODE_NONE)
         ms, smp = 0.0, 0
         for k in range(2):
             rs.render_frame(uniforms(args.warmup + k), pkg.MODE_NONE)
             ms += rs.timings().trace_ms
             smp += rs.frame_stats().samples_traced
+        rs_name = rs.kernel_name()
         rs.close()
         strict = {"conv": 0, "value": smp / ms / 1e3, "unit": "Msamples/s (trace kernel, device)", "trace_ms_per_step": ms / 2,
                   "roofline_frac": fmin_per_sample * smp / (ms / 1e3) / 1e12 / NOMINAL_FP32_TFLOPS,
-                  "note": "same kernel source, one IEEE rounding per WGSL operator; bit-exact against the oracle (tests/test_gpu_parity.py)"}
+                  "kernel": rs_name,
+                  "note": "one IEEE rounding per WGSL operator; bit-exact against oracle/_ref (config.parity, tests/test_gpu_parity.py)"}
 
     value = samples_total / (dev_ms / 1e3) / 1e6
     line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
@@ -374,10 +495,9 @@ def ours(args):
                                       2: "device-native: FFMA contraction + MUFU rcp/rsqrt/sqrt/sin/cos, within north_star tolerances (tests/test_gpu_native.py)"}[args.conv],
                        "stripe_rows": args.stripe_rows,
                        "l2": "256 MiB flush between timed steps" if small else "frame buffers (3 x %d MB) exceed the 126 MB L2" % (frame_bytes >> 20),
-                       "parallelism": f"rows x{world}"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "strict": strict}
-    if ranks:
-        line["ranks"] = ranks
+                       "parallelism": f"rows x{world}", "parity": parity, "strict": strict, "ranks": ranks},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "roofline_quantise": roofline_q,
+            "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)
     sr.close()
     if world > 1:
@@ -401,6 +521,8 @@ def main():
     ap.add_argument("--count-stride", type=int, default=24, help="instrumented kernel runs on every n-th row")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity check of the named configuration (config.parity)")
+    ap.add_argument("--parity-pixels", type=int, default=20000)
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

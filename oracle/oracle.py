@@ -118,7 +118,7 @@ _fast = None
 
 
 def fast_lib() -> C.CDLL:
-    """liboracle_fast.so (-O3 -march=native -ffp-contract=off): same sources, same bits (tested), used by the
+    """liboracle_fast.so (-O3 -march=x86-64-v3 -ffp-contract=off): same sources, same bits (tested), used by the
     TIMED cpu_baseline / --impl reference legs only."""
     global _fast
     if _fast is None:
@@ -205,6 +205,22 @@ def ref_render(prims: np.ndarray, u: np.ndarray, accumulation: np.ndarray | None
     if rc != 0:
         raise ValueError("ref_render: bad arguments")
     return {"accumulation": accumulation, "pixels": pixels, "variance": var}
+
+
+def samples_from_variance(var: np.ndarray, spp: int) -> int:
+    """ray_color calls a frame made, re-derived from the variance buffer it left behind: every pixel traces
+    base = max(4, spp / 4) samples (shader.wgsl:513) plus, when variance > 10 and base < spp, min(spp - base,
+    u32(variance * 50)) extra ones (:561-562).  The transliterated shader has no counter; the hand oracle's own
+    `samples_traced` equals this (tests/test_oracle_ref.py)."""
+    base = max(4, int(spp) // 4)
+    v = np.ascontiguousarray(var["variance"], np.float32)
+    extra = np.zeros(len(v), np.int64)
+    if base < spp:
+        m = v > np.float32(10.0)
+        prod = (v[m] * np.float32(50.0)).astype(np.float32)
+        u = np.where(prod >= np.float32(4294967296.0), np.float32(4294967040.0), prod).astype(np.uint32).astype(np.int64)
+        extra[m] = np.minimum(int(spp) - base, u)
+    return int(len(v) * base + extra.sum())
 
 
 def ref_pcg_hash(v: int) -> int:
