@@ -165,22 +165,27 @@ __device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool
 #ifndef TRT_V_CAMFOLD
 #define TRT_V_CAMFOLD 1
 #endif
-// TRT_V_SHIFT_T (candidate, not measured yet): plane / triangle accept tests of the unrolled small-scene scan on
-// t' = t - t_min compared as unsigned integers (one compare instead of two and a predicate merge)
+// TRT_V_SHIFT_T: plane / triangle accept tests of the unrolled small-scene scan on t' = t - t_min compared as unsigned
+// integers (one compare instead of two and a predicate merge).  t' carries one more rounding than t (within WGSL's
+// latitude for the division it replaces).  B200 A/B frame: 39.94 -> 38.83 ms; the deviation from the strict frame is
+// unchanged (C3 parity subset: 1726 of 20 000 pixels over 1e-4 with and without it; profiles/r2_ab_variants.txt).
 #ifndef TRT_V_SHIFT_T
-#define TRT_V_SHIFT_T 0
+#define TRT_V_SHIFT_T 1
 #endif
 // TRT_V_KEY: the bound of the unrolled small-scene scan as ONE ordered key -- the bits of t' = t - t_min with the low
 // index bits replaced by the primitive index.  For t' >= +0 the float order is the unsigned order, a negative or NaN t'
 // sorts above every valid bound, so `t_min <= t < closest, remember who` is FFMA + LOP3 + (half a) VIMNMX3.U32 per plane
 // (as written: FFMA + 2 FSETP + PLOP3 + FSEL + SEL).  Equal keys keep the lower index = the first primitive in scan
 // order (shader.wgsl:279).  Cost: t is known to 2^-19 relative (4 index bits) instead of 2^-24 -- conv 2 only,
-// inside its tolerance (tests/test_gpu_native.py).  B200, A/B frame: 39.94 -> 38.65 ms (profiles/r2_ab_variants.txt).
+// inside its tolerance (tests/test_gpu_native.py).  B200, A/B frame: 39.94 -> 38.65 ms, i.e. 0.5 % better than
+// TRT_V_SHIFT_T -- but the coarser t DOUBLES the deviation from the strict frame on deep paths (C3 parity subset: 3893
+// of 20 000 pixels over 1e-4 against 1726, RMSE 0.34 of the noise floor against 0.23; profiles/r2_ab_variants.txt):
+// measured, not adopted.
 #ifndef TRT_V_KEY
-#define TRT_V_KEY 1
+#define TRT_V_KEY 0
 #endif
 // TRT_V_NO_RENORM: cosine_hemisphere_unit returns u*x + v*y + w*z without the final normalize (:334): (u, v, w) is
-// orthonormal and x^2 + y^2 + z^2 = 1 up to rounding, so the length is 1 +- a few ulp already.  38.65 -> 38.41 ms.
+// orthonormal and x^2 + y^2 + z^2 = 1 up to rounding, so the length is 1 +- a few ulp already.  -0.6 % (38.65 -> 38.41 ms).
 #ifndef TRT_V_NO_RENORM
 #define TRT_V_NO_RENORM 1
 #endif
