@@ -10,7 +10,7 @@ configs[2] "c3": Cornell box 3840x2160, 1024 spp, max_depth 32, truecolor stream
 the N GPUs (the configuration the metric "Cornell Box at 1/2/4/8 B200" is quoted on; total work is
 fixed as N grows => "scaling": "strong").  --workload c1|c2|c4 select the other configs.
 
-`value`  : device-resident (scene + buffers in HBM; trace + accumulate + gather + quantise).
+`value`  : device-resident (scene + buffers in HBM; trace + accumulate + quantise of the own rows + row-length all-gather).
 `e2e`    : the same through trt_render_frame with HOST buffers: uniforms in, byte stream out (pinned).
 `roofline`: trace kernel, FP32: achieved = F_min (algorithmic flops) / CUDA-event time.
 `roofline_quantise`: the on-device quantiser (pack + scan + emit), algorithmic bytes / its CUDA-event time / HBM peak.
@@ -39,7 +39,7 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as graft  # noqa: E402
 
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # 74.45: SMs x lanes x 2 x max clock
-QUANT_KERNELS = "quant_pack_kernel + quant_scan_kernel + quant_emit_kernel"
+QUANT_KERNELS = "quant_pack_kernel + quant_scan_kernel + quant_emit_kernel + quant_row_len_kernel"
 
 
 def workload(name, O, args):
@@ -324,11 +324,11 @@ def ours(args):
         evs[k][1].record(stream)
         # per-step statistics are read back after the step's stop event (they sync the stream)
         t = sr.r.timings()
-        st = sr.step_times()                          # this rank's trace kernel alone / pack + gather / quantise
+        st = sr.step_times()                          # this rank's trace kernel alone / row-length exchange / quantise of its rows
         trace_ms.append(st[0])
         combine_ms.append(st[1] + st[2])
         quant_ms.append(st[2])
-        launches += t.kernel_launches                 # trace + pack_rows + 3 quantise kernels (rank 0)
+        launches += t.kernel_launches                 # order + trace + 3 quantise kernels + row lengths
         samples_local += sr.r.frame_stats().samples_traced
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -345,7 +345,7 @@ def ours(args):
                                                device=f"cuda:{local}"))
         ranks = {"trace_ms": [round(v[0].item(), 2) for v in per_rank],
                  "combine_ms_rank0": round(per_rank[0][1].item(), 2),
-                 "note": "per rank: its trace kernel alone; rank 0: pack + gather (waits for the slowest rank) + quantise"}
+                 "note": "per rank: its trace kernel alone; rank 0: quantise of its rows + all-gather of the row lengths (waits for the slowest rank)"}
     else:
         samples_total, trace_sum_max = float(samples_local), float(sum(trace_ms))
         ranks = None
@@ -374,24 +374,19 @@ def ours(args):
         e2e = {"value": s_e2e / t_e2e / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 160,
                "d2h_bytes_per_step": out_bytes // args.steps + 8, "ms_per_step": t_e2e / args.steps * 1e3}
     else:
-        # N > 1: the gathered frame is quantised on rank 0 and its byte stream read back to host memory
-        cap = w * h * 26 + 2 * h + 64
-        host = pkg.api._P()
-        if rank == 0:
-            assert pkg.api.lib().trt_alloc_host(cap, __import__("ctypes").byref(host)) == 0
+        # N > 1: every rank quantises its rows and copies them over its own PCIe link to their place in the host buffer
+        # the ranks share; the frame is on the host when the slowest rank's copy has landed (barrier)
         barrier()
         t0 = time.perf_counter()
         out_bytes = 0
         for k in range(args.steps):
             sr.step(uniforms(args.warmup + k), mode)
-            if rank == 0:
-                out_bytes += sr.r.read_stream_into(host, cap)      # blocks until the bytes are in host memory
+            out_bytes += sr.read_stream()                          # blocks until this rank's rows are in host memory
             barrier()
         t_e2e = time.perf_counter() - t0
-        if rank == 0:
-            pkg.api.lib().trt_free_host(host)
         e2e = {"value": samples_total / t_e2e / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 160 * world,
-               "d2h_bytes_per_step": out_bytes // args.steps + 8, "ms_per_step": t_e2e / args.steps * 1e3}
+               "d2h_bytes_per_step": out_bytes // args.steps + 4 * sr.max_rows * world * world, "ms_per_step": t_e2e / args.steps * 1e3,
+               "note": "d2h = the frame's byte stream (each rank its own rows, its own link) + the all-gathered row-length table on every rank"}
 
     if rank != 0:
         sr.close()

@@ -62,6 +62,7 @@ const _: () = assert!(std::mem::size_of::<trt_variance>() == 8);
 
 #[repr(C)] pub struct trt_ctx { _private: [u8; 0] }
 #[repr(C)] pub struct trt_scene { _private: [u8; 0] }
+#[repr(C)] pub struct trt_multi { _private: [u8; 0] }
 
 #[repr(C)] #[derive(Clone, Copy, Default, Debug)]
 pub struct trt_config {
@@ -98,7 +99,7 @@ pub struct trt_scene_info {
 pub struct trt_run_options {
     pub width: u32, pub height: u32, pub frames: u32, pub seed: u32, pub has_seed: u32,
     pub keys: *const c_char, pub out_path: *const c_char,
-    pub device: i32, pub conv: u32, pub quiet: u32, pub batch_frames: u32,
+    pub device: i32, pub conv: u32, pub quiet: u32, pub batch_frames: u32, pub gpus: u32, pub pipeline: u32,
 }
 
 extern "C" {
@@ -133,6 +134,24 @@ extern "C" {
                                  shard_count: u32, stripe_rows: u32, mode: c_int, len_needed_or_null: *mut usize) -> c_int;
     pub fn trt_alloc_host(bytes: usize, out: *mut *mut c_void) -> c_int;
     pub fn trt_free_host(p: *mut c_void);
+    pub fn trt_host_register(p: *mut c_void, bytes: usize) -> c_int;
+    pub fn trt_host_unregister(p: *mut c_void) -> c_int;
+    pub fn trt_quantise_rows_async(ctx: *mut trt_ctx, mode: c_int) -> c_int;
+    pub fn trt_row_lengths(ctx: *mut trt_ctx, out: *mut u32, cap: u32, n_rows: *mut u32) -> c_int;
+    pub fn trt_read_stream_rows(ctx: *mut trt_ctx, host_base: *mut u8, cap: usize, row_off: *const u64, height: u32, wait: c_int) -> c_int;
+    pub fn trt_frame_submit(ctx: *mut trt_ctx, u: *const trt_uniforms, mode: c_int) -> c_int;
+    pub fn trt_frame_collect(ctx: *mut trt_ctx, out: *mut u8, cap: usize, len: *mut usize) -> c_int;
+    pub fn trt_multi_create(devices: *const i32, n_devices: u32, cfg: *const trt_config, out: *mut *mut trt_multi) -> c_int;
+    pub fn trt_multi_destroy(m: *mut trt_multi);
+    pub fn trt_multi_last_error(m: *const trt_multi) -> *const c_char;
+    pub fn trt_multi_size(m: *const trt_multi) -> u32;
+    pub fn trt_multi_context(m: *mut trt_multi, i: u32) -> *mut trt_ctx;
+    pub fn trt_multi_upload_scene(m: *mut trt_multi, prims: *const trt_primitive, count: u32) -> c_int;
+    pub fn trt_multi_render_frame(m: *mut trt_multi, u: *const trt_uniforms, mode: c_int, out: *mut u8, cap: usize, len: *mut usize) -> c_int;
+    pub fn trt_multi_read_pixels(m: *mut trt_multi, dst4: *mut f32, n_pixels: usize) -> c_int;
+    pub fn trt_multi_read_variance(m: *mut trt_multi, dst: *mut trt_variance, n_pixels: usize) -> c_int;
+    pub fn trt_multi_get_frame_stats(m: *mut trt_multi, out: *mut trt_frame_stats) -> c_int;
+    pub fn trt_multi_get_timings(m: *mut trt_multi, out: *mut trt_timings) -> c_int;
     pub fn trt_camera_default(cam: *mut trt_camera);
     pub fn trt_camera_vectors(cam: *const trt_camera, forward: *mut trt_vec3, right: *mut trt_vec3, up: *mut trt_vec3);
     pub fn trt_camera_key(cam: *mut trt_camera, key: c_int) -> c_int;
@@ -205,12 +224,47 @@ impl Tracer {
 }
 impl Drop for Tracer { fn drop(&mut self) { unsafe { trt_destroy(self.ctx) } } }
 
+/// The same frame over several GPUs of this process (`trt_multi_*`): what `run()` holds instead of a `Tracer` when
+/// it is given more than one device.  The rows block is byte-identical to a single-GPU frame.
+pub struct MultiTracer { m: *mut trt_multi, out: *mut u8, cap: usize }
+
+impl MultiTracer {
+    fn err(m: *const trt_multi, code: c_int) -> Error {
+        let message = unsafe { CStr::from_ptr(trt_multi_last_error(m)) }.to_string_lossy().into_owned();
+        Error { code, message }
+    }
+    pub fn new(devices: &[i32], max_width: u32, max_height: u32, conv: u32) -> Result<Self, Error> {
+        let cfg = trt_config { abi_version: TRT_ABI_VERSION, max_width, max_height, conv, ..Default::default() };
+        let mut m = std::ptr::null_mut();
+        let rc = unsafe { trt_multi_create(devices.as_ptr(), devices.len() as u32, &cfg, &mut m) };
+        if rc != TRT_OK { return Err(Self::err(std::ptr::null(), rc)); }
+        let cap = max_width as usize * max_height as usize * 26 + max_height as usize * 2 + 64;
+        let mut out: *mut c_void = std::ptr::null_mut();
+        // pinned memory: the GPUs copy their rows concurrently, each over its own PCIe link
+        if unsafe { trt_alloc_host(cap, &mut out) } != TRT_OK { unsafe { trt_multi_destroy(m) }; return Err(Error { code: TRT_ERR_NOMEM, message: "pinned host buffer".into() }); }
+        Ok(MultiTracer { m, out: out as *mut u8, cap })
+    }
+    pub fn upload_scene<P: Copy>(&mut self, prims: &[P]) -> Result<(), Error> {
+        assert_eq!(std::mem::size_of::<P>(), 180, "Primitive must be the 180-byte #[repr(C)] record");
+        let rc = unsafe { trt_multi_upload_scene(self.m, prims.as_ptr() as *const trt_primitive, prims.len() as u32) };
+        if rc == TRT_OK { Ok(()) } else { Err(Self::err(self.m, rc)) }
+    }
+    pub fn render_frame<U: Copy>(&mut self, uniforms: &U, full_color: bool) -> Result<&[u8], Error> {
+        assert_eq!(std::mem::size_of::<U>(), 160, "Uniforms must be the 160-byte #[repr(C)] record");
+        let mode = if full_color { TRT_MODE_TRUECOLOR } else { TRT_MODE_ASCII };
+        let mut len = 0usize;
+        let rc = unsafe { trt_multi_render_frame(self.m, uniforms as *const U as *const trt_uniforms, mode, self.out, self.cap, &mut len) };
+        if rc == TRT_OK { Ok(unsafe { std::slice::from_raw_parts(self.out, len) }) } else { Err(Self::err(self.m, rc)) }
+    }
+}
+impl Drop for MultiTracer { fn drop(&mut self) { unsafe { trt_free_host(self.out as *mut c_void); trt_multi_destroy(self.m) } } }
+
 /// The reference's `pub async fn run(full_color, verbose, scene_path)` (`src/lib.rs:100`) executed entirely by the
 /// native library (scene parsing, camera, loop, terminal handling): for hosts that only want the entry point.
 pub fn run(full_color: bool, verbose: bool, scene_path: Option<&str>) -> Result<(), Error> {
     let path = scene_path.map(|p| std::ffi::CString::new(p).expect("path contains NUL"));
     let opts = trt_run_options { width: 0, height: 0, frames: 0, seed: 0, has_seed: 0, keys: std::ptr::null(), out_path: std::ptr::null(),
-                                 device: 0, conv: TRT_CONV_NATIVE, quiet: 0, batch_frames: 0 };
+                                 device: 0, conv: TRT_CONV_NATIVE, quiet: 0, batch_frames: 0, gpus: 0, pipeline: 0 };
     let rc = unsafe { trt_run(full_color as c_int, verbose as c_int, path.as_ref().map_or(std::ptr::null(), |p| p.as_ptr()), &opts) };
     if rc == TRT_OK { Ok(()) } else { Err(Error { code: rc, message: "trt_run failed (see stderr)".into() }) }
 }

@@ -185,7 +185,8 @@ int trt_selftest_div3(int device, uint64_t n_cases, uint32_t seed, int distribut
 
 /* multi-GPU plumbing: raw device pointers of this context's buffers so that the host driver can
  * hand them to NCCL (gather of the shards' pixel rows), and a quantise that reads a caller-owned
- * device frame.  which: 0 pixels (float4), 1 accumulation, 2 variance, 3 byte stream. */
+ * device frame.  which: 0 pixels (float4), 1 accumulation, 2 variance, 3 byte stream, 4 frame statistics,
+ * 5 row lengths of the last trt_quantise_rows_async (u32 per local row). */
 int trt_device_buffer(trt_ctx *ctx, int which, void **dptr, size_t *bytes);
 int trt_cuda_stream(trt_ctx *ctx, void **stream);
 /* rows this shard owns, ascending; returns the count (writes at most cap entries) */
@@ -204,6 +205,44 @@ int trt_quantise_gathered(trt_ctx *ctx, const void *d_gathered, size_t block_str
 /* pinned host memory for `out` buffers (optional; any host pointer works) */
 int trt_alloc_host(size_t bytes, void **out);
 void trt_free_host(void *p);
+/* page-lock memory the caller owns (e.g. a POSIX shared-memory segment several ranks copy their rows into) */
+int trt_host_register(void *p, size_t bytes);
+int trt_host_unregister(void *p);
+
+/* ---- row-addressed streams (sharded frames without moving a pixel) -------------------------------
+ * The frame's stream is its rows back to back (lib.rs:503-532) and a row's bytes depend on that row only: every
+ * shard quantises ITS rows (trt_quantise_rows_async: stream of the rows it owns, in ascending row order, plus the
+ * byte length of each -- device buffer 5, u32 per local row), the lengths are exchanged (4 B per row instead of
+ * 16 B per pixel), and every shard copies its rows device -> host straight to their place in ONE host buffer
+ * (trt_read_stream_rows; row_off = height + 1 byte offsets of the whole frame's rows, row_off[height] = total).
+ * wait == 0: the copies are queued on the context's stream (trt_sync to wait). */
+int trt_quantise_rows_async(trt_ctx *ctx, int mode);
+int trt_row_lengths(trt_ctx *ctx, uint32_t *out, uint32_t cap, uint32_t *n_rows);
+int trt_read_stream_rows(trt_ctx *ctx, uint8_t *host_base, size_t cap, const uint64_t *row_off, uint32_t height, int wait);
+
+/* ---- pipelined frames: replaces the strictly serial dispatch / map+poll / format / print of lib.rs:442-477,
+ * 503-545.  Up to two frames in flight: submit queues trace + quantise and returns; collect hands out the OLDEST
+ * submitted frame, its device -> host copy running on a second stream while the next frame is being traced.  Same
+ * frames, same order, same bytes as trt_render_frame called once per frame. */
+int trt_frame_submit(trt_ctx *ctx, const trt_uniforms *u, int mode);
+int trt_frame_collect(trt_ctx *ctx, uint8_t *out, size_t cap, size_t *len);
+
+/* ---- one frame over several GPUs of one process (the reference has one device: lib.rs:248-250) --------
+ * One row-sharded context per device (cfg->device / shard_* are filled in; stripe_rows 0 = 4).  render_frame has
+ * trt_render_frame's contract: blocks until the assembled stream is in `out` (pinned memory lets the GPUs copy
+ * concurrently); the stream is byte-identical to a single-GPU frame. */
+typedef struct trt_multi trt_multi;
+int trt_multi_create(const int32_t *devices, uint32_t n_devices, const trt_config *cfg, trt_multi **out);
+void trt_multi_destroy(trt_multi *m);
+const char *trt_multi_last_error(const trt_multi *m);
+uint32_t trt_multi_size(const trt_multi *m);
+trt_ctx *trt_multi_context(trt_multi *m, uint32_t i);
+int trt_multi_upload_scene(trt_multi *m, const trt_primitive *prims, uint32_t count);
+int trt_multi_render_frame(trt_multi *m, const trt_uniforms *u, int mode, uint8_t *out, size_t cap, size_t *len);
+int trt_multi_read_pixels(trt_multi *m, float *dst4, size_t n_pixels);
+int trt_multi_read_variance(trt_multi *m, trt_variance *dst, size_t n_pixels);
+int trt_multi_get_frame_stats(trt_multi *m, trt_frame_stats *out);
+int trt_multi_get_timings(trt_multi *m, trt_timings *out);
 
 /* ---- host logic of the reference, restated natively (no GPU needed) --------------------------- */
 
@@ -253,6 +292,9 @@ typedef struct trt_run_options {
     uint32_t batch_frames;        /* > 1: while the camera is still, render this many frames per GPU round trip
                                    * (trt_render_frames) and show the last one; 0 / 1: one frame per round trip as
                                    * the reference does */
+    uint32_t gpus;                /* > 1: every frame row-sharded over devices device .. device + gpus - 1 (trt_multi) */
+    uint32_t pipeline;            /* 1: frame f is copied back and written while frame f + 1 is traced
+                                   * (trt_frame_submit / trt_frame_collect); same frames, same bytes, same order */
 } trt_run_options;
 int trt_run(int full_color, int verbose, const char *scene_path_or_null, const trt_run_options *opts);
 

@@ -7,5 +7,5 @@ The product is the native library `libtrt_b200.so` (CUDA kernels for sm_100a beh
 include/trt_b200.h); `api` is its ctypes face and `multigpu` the torch.distributed/NCCL driver.
 """
 from . import api  # noqa: F401
-from .api import (Camera, Renderer, Scene, TrtError, Uniforms, run,  # noqa: F401
+from .api import (Camera, MultiRenderer, Renderer, Scene, TrtError, Uniforms, run,  # noqa: F401
                   CONV_AS_WRITTEN, CONV_FUSED, CONV_NATIVE, MODE_ASCII, MODE_TRUECOLOR, MODE_NONE)

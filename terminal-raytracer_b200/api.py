@@ -91,7 +91,8 @@ class SceneInfo(C.Structure):
 class RunOptions(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("frames", C.c_uint32), ("seed", C.c_uint32),
                 ("has_seed", C.c_uint32), ("keys", C.c_char_p), ("out_path", C.c_char_p), ("device", C.c_int32),
-                ("conv", C.c_uint32), ("quiet", C.c_uint32), ("batch_frames", C.c_uint32)]
+                ("conv", C.c_uint32), ("quiet", C.c_uint32), ("batch_frames", C.c_uint32), ("gpus", C.c_uint32),
+                ("pipeline", C.c_uint32)]
 
 
 assert C.sizeof(Vec3) == 16 and C.sizeof(Primitive) == 180 and C.sizeof(Uniforms) == 160
@@ -129,6 +130,24 @@ SYMBOLS = {
                                         C.POINTER(C.c_size_t)]),
     "trt_alloc_host": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "trt_free_host": (None, [_P]),
+    "trt_host_register": (C.c_int, [_P, C.c_size_t]),
+    "trt_host_unregister": (C.c_int, [_P]),
+    "trt_quantise_rows_async": (C.c_int, [_P, C.c_int]),
+    "trt_row_lengths": (C.c_int, [_P, _P, C.c_uint32, C.POINTER(C.c_uint32)]),
+    "trt_read_stream_rows": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_uint32, C.c_int]),
+    "trt_frame_submit": (C.c_int, [_P, C.POINTER(Uniforms), C.c_int]),
+    "trt_frame_collect": (C.c_int, [_P, _P, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "trt_multi_create": (C.c_int, [C.POINTER(C.c_int32), C.c_uint32, C.POINTER(Config), C.POINTER(_P)]),
+    "trt_multi_destroy": (None, [_P]),
+    "trt_multi_last_error": (C.c_char_p, [_P]),
+    "trt_multi_size": (C.c_uint32, [_P]),
+    "trt_multi_context": (_P, [_P, C.c_uint32]),
+    "trt_multi_upload_scene": (C.c_int, [_P, _P, C.c_uint32]),
+    "trt_multi_render_frame": (C.c_int, [_P, C.POINTER(Uniforms), C.c_int, _P, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "trt_multi_read_pixels": (C.c_int, [_P, _P, C.c_size_t]),
+    "trt_multi_read_variance": (C.c_int, [_P, _P, C.c_size_t]),
+    "trt_multi_get_frame_stats": (C.c_int, [_P, C.POINTER(FrameStats)]),
+    "trt_multi_get_timings": (C.c_int, [_P, C.POINTER(Timings)]),
     "trt_camera_default": (None, [C.POINTER(CameraStruct)]),
     "trt_camera_vectors": (None, [C.POINTER(CameraStruct), C.POINTER(Vec3), C.POINTER(Vec3), C.POINTER(Vec3)]),
     "trt_camera_key": (C.c_int, [C.POINTER(CameraStruct), C.c_int]),
@@ -418,6 +437,36 @@ class Renderer:
         n = lib().trt_shard_rows(self.h, height, rows.ctypes.data, height)
         return rows[:n]
 
+    # ---- row-addressed streams (sharded frames without moving a pixel) ----
+    def quantise_rows_async(self, mode):
+        """Quantise the rows this context owns and compute every row's byte length (device buffer 5)."""
+        self._ck(lib().trt_quantise_rows_async(self.h, mode))
+
+    def row_lengths(self) -> np.ndarray:
+        """Byte length of each owned row of the last quantise_rows_async (waits for it)."""
+        out = np.zeros(max(1, self.size[1]), np.uint32)
+        n = C.c_uint32()
+        self._ck(lib().trt_row_lengths(self.h, out.ctypes.data, len(out), C.byref(n)))
+        return out[:n.value]
+
+    def read_stream_rows(self, host_ptr, cap, row_off: np.ndarray, wait=True):
+        """Copy the owned rows to host_ptr + row_off[y] (row_off: height + 1 uint64 offsets of the whole frame)."""
+        ro = np.ascontiguousarray(row_off, np.uint64)
+        self._ck(lib().trt_read_stream_rows(self.h, host_ptr, cap, ro.ctypes.data, len(ro) - 1, 1 if wait else 0))
+
+    # ---- pipelined frames ----
+    def frame_submit(self, u: Uniforms, mode):
+        self.size = (u.width, u.height)
+        self._ck(lib().trt_frame_submit(self.h, C.byref(u), mode))
+
+    def frame_collect(self) -> bytes:
+        w, h = self.size
+        cap = w * h * 26 + 2 * h + 64
+        p, _ = self._host_out(cap)
+        n = C.c_size_t()
+        self._ck(lib().trt_frame_collect(self.h, p, cap, C.byref(n)))
+        return C.string_at(p, n.value)
+
     def pack_shard_pixels(self, dptr, nbytes):
         self._ck(lib().trt_pack_shard_pixels(self.h, dptr, nbytes))
 
@@ -427,6 +476,86 @@ class Renderer:
                                              mode, C.byref(n) if want_len else None))
         self.size = (width, height)
         return n.value
+
+
+class MultiRenderer:
+    """One frame over several GPUs of THIS process (trt_multi_*): one row-sharded context per device; render_frame
+    returns the assembled byte stream, byte-identical to a single-GPU frame."""
+
+    def __init__(self, max_width, max_height, devices, conv=CONV_AS_WRITTEN, stripe_rows=4):
+        cfg = Config(abi_version=TRT_ABI_VERSION, device=0, max_width=max_width, max_height=max_height, conv=conv,
+                     stripe_rows=stripe_rows)
+        devs = (C.c_int32 * len(devices))(*devices)
+        self.h = _P()
+        rc = lib().trt_multi_create(devs, len(devices), C.byref(cfg), C.byref(self.h))
+        if rc:
+            self.h = None
+            raise TrtError(rc, lib().trt_multi_last_error(None).decode())
+        self._out = None
+        self.size = (0, 0)
+
+    def close(self):
+        if getattr(self, "h", None):
+            if self._out is not None:
+                lib().trt_free_host(self._out[0])
+                self._out = None
+            lib().trt_multi_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc:
+            raise TrtError(rc, lib().trt_multi_last_error(self.h).decode())
+
+    def __len__(self):
+        return int(lib().trt_multi_size(self.h))
+
+    def upload_scene(self, prims):
+        if isinstance(prims, Scene):
+            prims = prims.primitives()
+        a = np.ascontiguousarray(prims)
+        self._ck(lib().trt_multi_upload_scene(self.h, a.ctypes.data, a.nbytes // 180))
+
+    def render_frame(self, u: Uniforms, mode=MODE_ASCII) -> bytes:
+        self.size = (u.width, u.height)
+        if mode == MODE_NONE:
+            self._ck(lib().trt_multi_render_frame(self.h, C.byref(u), mode, None, 0, None))
+            return b""
+        cap = u.width * u.height * 26 + 2 * u.height + 64
+        if self._out is None or self._out[1] < cap:
+            if self._out is not None:
+                lib().trt_free_host(self._out[0])
+            p = _P()
+            rc = lib().trt_alloc_host(cap, C.byref(p))
+            if rc:
+                raise TrtError(rc, lib().trt_last_error(None).decode())
+            self._out = (p, cap)
+        n = C.c_size_t()
+        self._ck(lib().trt_multi_render_frame(self.h, C.byref(u), mode, self._out[0], cap, C.byref(n)))
+        return C.string_at(self._out[0], n.value)
+
+    def read_pixels(self):
+        w, h = self.size
+        a = np.zeros((w * h, 4), np.float32)
+        self._ck(lib().trt_multi_read_pixels(self.h, a.ctypes.data, w * h))
+        return a
+
+    def read_variance(self):
+        w, h = self.size
+        a = np.zeros(w * h, np.dtype([("variance", "<f4"), ("sample_count", "<u4")]))
+        self._ck(lib().trt_multi_read_variance(self.h, a.ctypes.data, w * h))
+        return a
+
+    def frame_stats(self) -> FrameStats:
+        st = FrameStats()
+        self._ck(lib().trt_multi_get_frame_stats(self.h, C.byref(st)))
+        return st
+
+    def timings(self) -> Timings:
+        t = Timings()
+        self._ck(lib().trt_multi_get_timings(self.h, C.byref(t)))
+        return t
 
 
 def shard_rows_of(shard_index, shard_count, stripe_rows, height) -> np.ndarray:
@@ -455,7 +584,7 @@ def measure_fp32_peak(device=0):
 
 def run(full_color: bool, verbose: bool, scene_path: str | None, **opts) -> int:
     """The reference's `run(full_color, verbose, scene_path)` (lib.rs:100); keyword extensions map to
-    trt_run_options (width, height, frames, seed, keys, out_path, device, conv, quiet, batch_frames)."""
+    trt_run_options (width, height, frames, seed, keys, out_path, device, conv, quiet, batch_frames, gpus, pipeline)."""
     o = RunOptions()
     for k, v in opts.items():
         if k == "seed":

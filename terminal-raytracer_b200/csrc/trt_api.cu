@@ -72,9 +72,28 @@ struct trt_ctx {
     uint64_t *d_block_off = nullptr;
     uint8_t *d_stream = nullptr;
     size_t stream_cap = 0;
-    uint64_t *h_len = nullptr;         // pinned
+    uint64_t *h_len = nullptr;         // pinned: [0] stream length, [2..3] lengths of the two pipelined frames, [4..5] frame statistics
     uint32_t last_q_blocks = 0;
     bool have_stream = false;
+    int last_mode = TRT_MODE_NONE;
+
+    // row-addressed stream: byte length of every row of the last quantised frame (local row order)
+    uint32_t *d_row_len = nullptr;
+    uint32_t *h_row_len = nullptr;     // pinned
+    cudaEvent_t ev_row_len = nullptr;
+    uint32_t row_len_rows = 0;
+    bool have_row_len = false;
+    // row table of trt_quantise_gathered (kept apart from this shard's own d_row_src), cached by layout
+    uint64_t *d_row_src_g = nullptr;
+    uint32_t g_w = 0, g_h = 0, g_shards = 0, g_stripe = 0;
+    size_t g_stride = 0;
+
+    // pipelined frames (trt_frame_submit / trt_frame_collect): a second device stream buffer, a copy stream
+    cudaStream_t copy_stream = nullptr;
+    uint8_t *d_stream2 = nullptr;
+    cudaEvent_t ev_q[2] = {nullptr, nullptr};
+    int pipe_mode[2] = {TRT_MODE_NONE, TRT_MODE_NONE};
+    uint32_t pipe_submitted = 0, pipe_collected = 0;
 
     // frame batch (trt_render_frames)
     float4 *d_batch_cur = nullptr;     // [frames of one chunk][local pixels]
@@ -127,9 +146,14 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_tiles, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
                     ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
-                    ctx->d_cost, ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream};
+                    ctx->d_cost, ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream,
+                    ctx->d_row_len, ctx->d_row_src_g, ctx->d_stream2};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
+    if (ctx->h_row_len) cudaFreeHost(ctx->h_row_len);
+    if (ctx->ev_row_len) cudaEventDestroy(ctx->ev_row_len);
+    for (auto &e : ctx->ev_q) if (e) cudaEventDestroy(e);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->h_batch_len) cudaFreeHost(ctx->h_batch_len);
     for (auto &e : ctx->ev) if (e) cudaEventDestroy(e);
     if (ctx->ev_stats) cudaEventDestroy(ctx->ev_stats);
@@ -182,6 +206,10 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         CK(cudaMalloc(&ctx->d_cost, ctx->max_pixels * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_map, (size_t)cfg->max_height * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_row_src, (size_t)cfg->max_height * sizeof(uint64_t)));
+        CK(cudaMalloc(&ctx->d_row_src_g, (size_t)cfg->max_height * sizeof(uint64_t)));
+        CK(cudaMalloc(&ctx->d_row_len, (size_t)cfg->max_height * sizeof(uint32_t)));
+        CK(cudaMallocHost(&ctx->h_row_len, (size_t)cfg->max_height * sizeof(uint32_t)));
+        CK(cudaEventCreateWithFlags(&ctx->ev_row_len, cudaEventDisableTiming));
         CK(cudaMalloc(&ctx->d_packed, ctx->max_pixels * sizeof(uint32_t)));
         const size_t nb = (ctx->max_pixels + TRT_Q_BLOCK - 1) / TRT_Q_BLOCK;
         CK(cudaMalloc(&ctx->d_block_len, nb * sizeof(uint32_t)));
@@ -189,6 +217,7 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         ctx->stream_cap = ctx->max_pixels * 26 + (size_t)cfg->max_height * 2 + 64;
         CK(cudaMalloc(&ctx->d_stream, ctx->stream_cap));
         CK(cudaMallocHost(&ctx->h_len, 64));
+        memset(ctx->h_len, 0, 64);
         CK(cudaStreamSynchronize(ctx->stream));
         return TRT_OK;
     }();
@@ -593,6 +622,8 @@ static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_
         CK(cudaMemsetAsync(ctx->d_block_off, 0, sizeof(uint64_t), ctx->stream));
     }
     ctx->last_q_blocks = q.n_blocks;
+    ctx->last_mode = mode;
+    ctx->have_row_len = false;
     CK(cudaMemcpyAsync(h_len ? h_len : ctx->h_len, ctx->d_block_off + q.n_blocks, sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->stream));
     ctx->have_stream = d_out == nullptr;
     return TRT_OK;
@@ -621,25 +652,151 @@ extern "C" int trt_quantise_gathered(trt_ctx *ctx, const void *d_gathered, size_
     if (height > ctx->cfg.max_height || (size_t)width * height > ctx->max_pixels || block_stride_bytes % sizeof(float4))
         return fail(ctx, TRT_ERR_INVALID, "quantise_gathered: frame exceeds the context's capacity");
     CK(cudaSetDevice(ctx->device));
-    // global row y lives in block (stripe % shard_count) at local row index = (rows of that shard below y)
-    std::vector<uint64_t> src(height);
-    std::vector<uint32_t> local(shard_count, 0);
-    for (uint32_t y = 0; y < height; y++) {
-        const uint32_t owner = (y / stripe_rows) % shard_count;
-        src[y] = (uint64_t)owner * (block_stride_bytes / sizeof(float4)) + (uint64_t)local[owner] * width;
-        local[owner]++;
+    // global row y lives in block (stripe % shard_count) at local row index = (rows of that shard below y).  The table
+    // lives in its own buffer (this shard's d_row_src stays valid) and is uploaded once per layout.
+    if (ctx->g_w != width || ctx->g_h != height || ctx->g_shards != shard_count || ctx->g_stripe != stripe_rows ||
+        ctx->g_stride != block_stride_bytes) {
+        std::vector<uint64_t> src(height);
+        std::vector<uint32_t> local(shard_count, 0);
+        for (uint32_t y = 0; y < height; y++) {
+            const uint32_t owner = (y / stripe_rows) % shard_count;
+            src[y] = (uint64_t)owner * (block_stride_bytes / sizeof(float4)) + (uint64_t)local[owner] * width;
+            local[owner]++;
+        }
+        CK(cudaStreamSynchronize(ctx->stream));
+        CK(cudaMemcpy(ctx->d_row_src_g, src.data(), height * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        ctx->g_w = width; ctx->g_h = height; ctx->g_shards = shard_count; ctx->g_stripe = stripe_rows; ctx->g_stride = block_stride_bytes;
     }
-    CK(cudaStreamSynchronize(ctx->stream));
-    CK(cudaMemcpy(ctx->d_row_src, src.data(), height * sizeof(uint64_t), cudaMemcpyHostToDevice));
-    ctx->rows_height = 0;      // d_row_src no longer describes this shard's rows
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
-    int rc = launch_quantise(ctx, (const float4 *)d_gathered, ctx->d_row_src, width, height, mode);
+    int rc = launch_quantise(ctx, (const float4 *)d_gathered, ctx->d_row_src_g, width, height, mode);
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     if (len_needed) {
         CK(cudaStreamSynchronize(ctx->stream));
         *len_needed = (size_t)*ctx->h_len;
     }
+    return TRT_OK;
+}
+
+// ---- row-addressed streams ---------------------------------------------------------------------------
+// A frame's byte stream is its rows back to back (lib.rs:503-532), and a row's bytes depend on that row's pixels
+// only.  So a sharded frame needs no pixel exchange at all: every shard quantises ITS rows on its GPU, publishes the
+// byte length of each (4 B per row), and once the lengths of all rows are known -- one tiny all-gather between
+// processes, or a host loop inside one -- every shard copies its rows device -> host over its own PCIe link, straight
+// to their final place in one host buffer.
+extern "C" int trt_quantise_rows_async(trt_ctx *ctx, int mode) {
+    if (!ctx) return TRT_ERR_INVALID;
+    int rc = trt_quantise_async(ctx, mode, nullptr);
+    if (rc) return rc;
+    const uint32_t rows = (uint32_t)ctx->rows.size();
+    if (rows) {
+        quant_row_len_kernel<<<(rows + 7u) / 8u, 256, 0, ctx->stream>>>(ctx->d_packed, ctx->last_u.width, rows, mode, ctx->d_row_len);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(ctx->h_row_len, ctx->d_row_len, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaEventRecord(ctx->ev_row_len, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    ctx->row_len_rows = rows;
+    ctx->have_row_len = true;
+    return TRT_OK;
+}
+
+extern "C" int trt_row_lengths(trt_ctx *ctx, uint32_t *out, uint32_t cap, uint32_t *n_rows) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (!ctx->have_row_len) return fail(ctx, TRT_ERR_INVALID, "row_lengths before trt_quantise_rows_async");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventSynchronize(ctx->ev_row_len));
+    if (n_rows) *n_rows = ctx->row_len_rows;
+    if (ctx->row_len_rows > cap || (!out && ctx->row_len_rows)) return fail(ctx, TRT_ERR_TOO_SMALL, "row_lengths: destination too small");
+    if (ctx->row_len_rows) memcpy(out, ctx->h_row_len, ctx->row_len_rows * sizeof(uint32_t));
+    return TRT_OK;
+}
+
+// Issues the copies of this shard's rows into host_base + row_off[y] (row_off: height + 1 offsets of the whole frame's
+// rows; runs of consecutive rows -- stripes -- are one copy each).  wait != 0: returns when the bytes have landed.
+extern "C" int trt_read_stream_rows(trt_ctx *ctx, uint8_t *host_base, size_t cap, const uint64_t *row_off, uint32_t height, int wait) {
+    if (!ctx || !row_off) return TRT_ERR_INVALID;
+    if (!ctx->have_row_len || !ctx->have_stream) return fail(ctx, TRT_ERR_INVALID, "read_stream_rows before trt_quantise_rows_async");
+    if (height != ctx->last_u.height) return fail(ctx, TRT_ERR_INVALID, "read_stream_rows: height differs from the last frame");
+    if (row_off[height] > cap || (!host_base && row_off[height])) return fail(ctx, TRT_ERR_TOO_SMALL, "read_stream_rows: output buffer too small for the frame stream");
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventSynchronize(ctx->ev_row_len));
+    uint64_t local = 0;
+    const size_t n = ctx->rows.size();
+    for (size_t i = 0; i < n;) {
+        size_t j = i;
+        uint64_t bytes = 0;
+        while (j < n && ctx->rows[j] == ctx->rows[i] + (uint32_t)(j - i)) { bytes += ctx->h_row_len[j]; j++; }
+        const uint32_t y0 = ctx->rows[i], y1 = ctx->rows[j - 1] + 1u;
+        if (row_off[y1] - row_off[y0] != bytes) return fail(ctx, TRT_ERR_INVALID, "read_stream_rows: row offsets disagree with this shard's row lengths");
+        if (bytes) CK(cudaMemcpyAsync(host_base + row_off[y0], ctx->d_stream + local, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        local += bytes;
+        i = j;
+    }
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (wait) CK(cudaStreamSynchronize(ctx->stream));
+    return TRT_OK;
+}
+
+extern "C" int trt_host_register(void *p, size_t bytes) {
+    if (!p || !bytes) return TRT_ERR_INVALID;
+    cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+    if (e != cudaSuccess) { g_create_err = std::string("trt_host_register: ") + cudaGetErrorString(e); cudaGetLastError(); return TRT_ERR_CUDA; }
+    return TRT_OK;
+}
+extern "C" int trt_host_unregister(void *p) {
+    if (!p) return TRT_ERR_INVALID;
+    cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) { cudaGetLastError(); return TRT_ERR_CUDA; }
+    return TRT_OK;
+}
+
+// ---- pipelined frames -----------------------------------------------------------------------------------
+// The reference's loop is strictly serial: dispatch, map + poll(Wait), format, print (lib.rs:442-477, 503-545).  Here
+// up to two frames are in flight: trt_frame_submit queues trace + quantise of frame f (into one of two device stream
+// buffers) and returns; trt_frame_collect hands out the OLDEST submitted frame -- its device -> host copy runs on a
+// second stream behind an event, so the copy, and whatever the caller does with the bytes (stdout), overlap the trace
+// of the frame submitted after it.  The frames, their order and their bytes are those of the serial loop.
+extern "C" int trt_frame_submit(trt_ctx *ctx, const trt_uniforms *u, int mode) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (mode != TRT_MODE_ASCII && mode != TRT_MODE_TRUECOLOR) return fail(ctx, TRT_ERR_INVALID, "frame_submit: bad mode");
+    if (ctx->cfg.shard_count > 1u) return fail(ctx, TRT_ERR_INVALID, "frame_submit: not on a sharded context");
+    if (ctx->pipe_submitted - ctx->pipe_collected >= 2u) return fail(ctx, TRT_ERR_INVALID, "frame_submit: two frames already in flight (collect one)");
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (auto &e : ctx->ev_q) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        CK(cudaMalloc(&ctx->d_stream2, ctx->stream_cap));
+    }
+    const uint32_t slot = ctx->pipe_submitted & 1u;
+    // the slot's previous copy (frame f - 2) was waited for by its collect, so its buffer is free
+    int rc = trace_impl(ctx, u, 0u);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    rc = launch_quantise(ctx, ctx->d_pixels, nullptr, u->width, u->height, mode, slot ? ctx->d_stream2 : ctx->d_stream, ctx->stream_cap,
+                         ctx->h_len + 2 + slot);
+    if (rc) return rc;
+    ctx->have_stream = false;          // the plain read_stream path does not see pipelined frames
+    CK(cudaEventRecord(ctx->ev_q[slot], ctx->stream));
+    ctx->pipe_mode[slot] = mode;
+    ctx->pipe_submitted++;
+    return TRT_OK;
+}
+
+extern "C" int trt_frame_collect(trt_ctx *ctx, uint8_t *out, size_t cap, size_t *len) {
+    if (!ctx || !len) return TRT_ERR_INVALID;
+    if (ctx->pipe_submitted == ctx->pipe_collected) return fail(ctx, TRT_ERR_INVALID, "frame_collect: no frame in flight");
+    CK(cudaSetDevice(ctx->device));
+    const uint32_t slot = ctx->pipe_collected & 1u;
+    CK(cudaEventSynchronize(ctx->ev_q[slot]));
+    const size_t n = (size_t)ctx->h_len[2 + slot];
+    *len = n;
+    ctx->pipe_collected++;
+    if (n > ctx->stream_cap) return fail(ctx, TRT_ERR_INVALID, "internal: stream longer than its buffer");
+    if (n > cap || (!out && n)) return fail(ctx, TRT_ERR_TOO_SMALL, "output buffer too small for the frame stream");
+    if (n) CK(cudaMemcpyAsync(out, slot ? ctx->d_stream2 : ctx->d_stream, n, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    CK(cudaStreamSynchronize(ctx->copy_stream));
     return TRT_OK;
 }
 
@@ -892,7 +1049,8 @@ extern "C" int trt_device_buffer(trt_ctx *ctx, int which, void **dptr, size_t *b
         case 1: *dptr = ctx->d_accum; n = ctx->max_pixels * sizeof(float4); break;
         case 2: *dptr = ctx->d_variance; n = ctx->max_pixels * sizeof(trt_variance); break;
         case 3: *dptr = ctx->d_stream; n = ctx->stream_cap; break;
-        case 4: *dptr = ctx->d_stats; n = TRT_STATS_BYTES; break;      // frame statistics + the diagnostic words of a measurement build
+        case 4: *dptr = ctx->d_stats; n = TRT_STATS_BYTES; break;
+        case 5: *dptr = ctx->d_row_len; n = (size_t)ctx->cfg.max_height * sizeof(uint32_t); break;   // trt_quantise_rows_async      // frame statistics + the diagnostic words of a measurement build
         default: return fail(ctx, TRT_ERR_INVALID, "device_buffer: unknown buffer id");
     }
     if (bytes) *bytes = n;

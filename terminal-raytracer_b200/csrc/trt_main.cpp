@@ -34,6 +34,8 @@ int main(int argc, char **argv) {
         else if (a == "--native") o.conv = TRT_CONV_NATIVE;
         else if (a == "--batch" && next) o.batch_frames = (uint32_t)strtoul(next, nullptr, 10);
         else if (a == "--quiet") o.quiet = 1;
+        else if (a == "--gpus" && next) o.gpus = (uint32_t)strtoul(next, nullptr, 10);     // rows of every frame over N devices
+        else if (a == "--pipeline") o.pipeline = 1;                                        // overlap copy + stdout with the next frame's trace
     }
     if (threads <= 0) {                                                    // main.rs:18-19
         threads = (long)std::thread::hardware_concurrency();

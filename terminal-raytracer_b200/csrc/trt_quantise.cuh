@@ -189,4 +189,17 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_emit_kernel(QuantParams q) 
     for (uint32_t k = head + body + threadIdx.x; k < total; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
 }
 
+// Byte length of every row of the last quantised frame (one warp per row): what a shard publishes so that the rows of
+// all shards can be placed in one stream without moving a pixel (row-addressed streams, trt_api.cu).
+__global__ void __launch_bounds__(256) quant_row_len_kernel(const uint32_t *packed, uint32_t width, uint32_t rows, int mode,
+                                                            uint32_t *row_len) {
+    const uint32_t r = blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+    if (r >= rows) return;
+    const uint32_t *p = packed + (size_t)r * width;
+    uint32_t n = 0;
+    for (uint32_t x = lane; x < width; x += 32u) n += pixel_len(__ldg(&p[x]), mode, false);
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if (lane == 0) row_len[r] = n + 2u;                  // "\r\n" (lib.rs:527)
+}
+
 }  // namespace trt

@@ -103,16 +103,33 @@ extern "C" int trt_run(int full_color, int verbose, const char *scene_path, cons
     cfg.max_height = info.height;
     cfg.conv = opts.conv;
     trt_ctx *ctx = nullptr;
-    rc = trt_create(&cfg, &ctx);
-    if (rc != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(nullptr)); trt_scene_free(scene); if (sink != stdout) fclose(sink); return rc; }
-    rc = trt_upload_scene(ctx, prims, n_prims);
-    if (rc != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); trt_destroy(ctx); trt_scene_free(scene); if (sink != stdout) fclose(sink); return rc; }
-    if (verbose) fprintf(stderr, "%s: %u primitives, %ux%u, %u spp, depth %u\n", trt_version(), n_prims, info.width, info.height,
-                         info.samples_per_pixel, info.max_depth);
+    trt_multi *multi = nullptr;                                  // --gpus N: every frame row-sharded over N devices
+    if (opts.gpus > 1u) {
+        std::vector<int32_t> devs(opts.gpus);
+        // TRT_B200_MULTI_SAME_DEVICE=1 (tests on a one-GPU box): all shards on opts.device
+        const char *same = getenv("TRT_B200_MULTI_SAME_DEVICE");
+        for (uint32_t i = 0; i < opts.gpus; i++) devs[i] = opts.device + (same && *same == '1' ? 0 : (int32_t)i);
+        rc = trt_multi_create(devs.data(), opts.gpus, &cfg, &multi);
+        if (rc != TRT_OK) { fprintf(stderr, "%s\n", trt_multi_last_error(nullptr)); trt_scene_free(scene); if (sink != stdout) fclose(sink); return rc; }
+        rc = trt_multi_upload_scene(multi, prims, n_prims);
+        if (rc != TRT_OK) { fprintf(stderr, "%s\n", trt_multi_last_error(multi)); trt_multi_destroy(multi); trt_scene_free(scene); if (sink != stdout) fclose(sink); return rc; }
+    } else {
+        rc = trt_create(&cfg, &ctx);
+        if (rc != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(nullptr)); trt_scene_free(scene); if (sink != stdout) fclose(sink); return rc; }
+        rc = trt_upload_scene(ctx, prims, n_prims);
+        if (rc != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); trt_destroy(ctx); trt_scene_free(scene); if (sink != stdout) fclose(sink); return rc; }
+    }
+    if (verbose) fprintf(stderr, "%s: %u primitives, %ux%u, %u spp, depth %u, %u GPU(s)\n", trt_version(), n_prims, info.width, info.height,
+                         info.samples_per_pixel, info.max_depth, multi ? opts.gpus : 1u);
 
     const size_t cap = (size_t)info.width * info.height * 26 + (size_t)info.height * 2 + 64;
-    uint8_t *bytes = nullptr;
-    if (trt_alloc_host(cap, (void **)&bytes) != TRT_OK) { trt_destroy(ctx); trt_scene_free(scene); if (sink != stdout) fclose(sink); return TRT_ERR_NOMEM; }
+    uint8_t *bytes = nullptr, *bytes2 = nullptr;
+    if (trt_alloc_host(cap, (void **)&bytes) != TRT_OK) { if (ctx) trt_destroy(ctx); trt_multi_destroy(multi); trt_scene_free(scene); if (sink != stdout) fclose(sink); return TRT_ERR_NOMEM; }
+    // pipelined loop (one GPU, one frame per round trip): frame f is collected, written and flushed while frame f + 1
+    // is being traced; the displayed stream is the serial loop's, one frame later
+    const bool pipelined = opts.pipeline && !multi && opts.batch_frames <= 1u;
+    if (pipelined && trt_alloc_host(cap, (void **)&bytes2) != TRT_OK) bytes2 = nullptr;
+    struct Pending { bool live = false; uint32_t frame_count = 0; clk::time_point t_submit; } pending;
 
     std::vector<int> script;
     if (opts.keys) {
@@ -132,6 +149,21 @@ extern "C" int trt_run(int full_color, int verbose, const char *scene_path, cons
     const int mode = full_color ? TRT_MODE_TRUECOLOR : TRT_MODE_ASCII;
     size_t script_pos = 0;
     int status = TRT_OK;
+
+    // the frame still in flight of a pipelined loop (at exit, or when the loop goes idle)
+    auto flush_pending = [&]() {
+        if (!pending.live || status != TRT_OK) return;
+        pending.live = false;
+        size_t len = 0;
+        uint8_t *buf = (rendered & 1u) ? bytes2 : bytes;
+        status = trt_frame_collect(ctx, buf, cap, &len);
+        if (status != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); return; }
+        fputs("\x1b[1;1H", sink);
+        fwrite(buf, 1, len, sink);
+        if (!opts.quiet) fprintf(sink, "\x1b[%u;1HFrame: %u/%u | FPS: %.1f | GPU: %dms | CPU: %dms | Cleanup: %dms | Other: %dms | Total: %dms\r\n",
+                                 info.height + 1u, pending.frame_count, info.frames_to_accumulate, 0.0, 0, 0, 0, 0, 0);
+        fflush(sink);
+    };
 
     for (;;) {
         auto t_total = clk::now();
@@ -156,44 +188,67 @@ extern "C" int trt_run(int full_color, int verbose, const char *scene_path, cons
             }
             size_t len = 0;
             auto t_gpu = clk::now();
-            status = k == 1u ? trt_render_frame(ctx, &batch_u[0], mode, bytes, cap, &len)
-                             : trt_render_frames(ctx, batch_u.data(), k, mode, 0, bytes, cap, &len, nullptr);
-            if (status != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); break; }
-            const double gpu_ms = ms_since(t_gpu);
-            frame_count += k;                                    // lib.rs:457
-            rendered += k;
-            auto now = clk::now();
-            frame_times.push_back(std::chrono::duration<double>(now - last_frame).count());
-            last_frame = now;
-            if (frame_times.size() > 30) frame_times.pop_front();
-            double sum = 0.0;
-            for (double t : frame_times) sum += t;
-            const double fps = sum > 0.0 ? (double)frame_times.size() / sum : 0.0;
-
-            auto t_io = clk::now();
-            fputs("\x1b[1;1H", sink);                            // lib.rs:497
-            fwrite(bytes, 1, len, sink);                         // lib.rs:544
-            fflush(sink);
-            const double io_ms = ms_since(t_io);
-            const double total_ms = ms_since(t_total);
-            if (!opts.quiet) {                                   // lib.rs:551-558
-                double other = total_ms - gpu_ms - io_ms;
-                if (other < 0.0) other = 0.0;
-                fprintf(sink, "\x1b[%u;1HFrame: %u/%u | FPS: %.1f | GPU: %dms | CPU: %dms | Cleanup: %dms | Other: %dms | Total: %dms\r\n",
-                        info.height + 1u, frame_count, info.frames_to_accumulate, fps, (int)gpu_ms, 0, 0, (int)other, (int)total_ms);
+            // presents one finished frame: cursor home + rows (lib.rs:497,544) + status line (lib.rs:551-558)
+            auto present = [&](const uint8_t *data, size_t n, uint32_t shown_count, double gpu_ms) {
+                auto now = clk::now();
+                frame_times.push_back(std::chrono::duration<double>(now - last_frame).count());
+                last_frame = now;
+                if (frame_times.size() > 30) frame_times.pop_front();
+                double sum = 0.0;
+                for (double t : frame_times) sum += t;
+                const double fps = sum > 0.0 ? (double)frame_times.size() / sum : 0.0;
+                auto t_io = clk::now();
+                fputs("\x1b[1;1H", sink);                        // lib.rs:497
+                fwrite(data, 1, n, sink);                        // lib.rs:544
                 fflush(sink);
+                const double io_ms = ms_since(t_io);
+                const double total_ms = ms_since(t_total);
+                if (!opts.quiet) {                               // lib.rs:551-558
+                    double other = total_ms - gpu_ms - io_ms;
+                    if (other < 0.0) other = 0.0;
+                    fprintf(sink, "\x1b[%u;1HFrame: %u/%u | FPS: %.1f | GPU: %dms | CPU: %dms | Cleanup: %dms | Other: %dms | Total: %dms\r\n",
+                            info.height + 1u, shown_count, info.frames_to_accumulate, fps, (int)gpu_ms, 0, 0, (int)other, (int)total_ms);
+                    fflush(sink);
+                }
+            };
+            if (pipelined && bytes2) {
+                status = trt_frame_submit(ctx, &batch_u[0], mode);           // frame f: queued, not waited for
+                if (status != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); break; }
+                frame_count += 1;                                // lib.rs:457
+                rendered += 1;
+                if (pending.live) {                              // frame f - 1: copy + write overlap the trace of frame f
+                    uint8_t *buf = (rendered & 1u) ? bytes : bytes2;
+                    status = trt_frame_collect(ctx, buf, cap, &len);
+                    if (status != TRT_OK) { fprintf(stderr, "%s\n", trt_last_error(ctx)); break; }
+                    present(buf, len, pending.frame_count, std::chrono::duration<double, std::milli>(clk::now() - pending.t_submit).count());
+                }
+                pending.live = true; pending.frame_count = frame_count; pending.t_submit = t_gpu;
+            } else {
+                if (multi) status = trt_multi_render_frame(multi, &batch_u[0], mode, bytes, cap, &len);
+                else status = k == 1u ? trt_render_frame(ctx, &batch_u[0], mode, bytes, cap, &len)
+                                      : trt_render_frames(ctx, batch_u.data(), k, mode, 0, bytes, cap, &len, nullptr);
+                if (status != TRT_OK) { fprintf(stderr, "%s\n", multi ? trt_multi_last_error(multi) : trt_last_error(ctx)); break; }
+                const double gpu_ms = ms_since(t_gpu);
+                frame_count += k;                                // lib.rs:457
+                rendered += k;
+                present(bytes, len, frame_count, gpu_ms);
             }
             camera_moved = false;                                // lib.rs:560
         } else {
+            flush_pending();
+            if (status != TRT_OK) break;
             if (!tty && script_pos >= script.size()) break;      // headless: nothing more can happen
             std::this_thread::sleep_for(std::chrono::milliseconds(10));   // lib.rs:563
         }
     }
+    flush_pending();                                             // the last frame of a pipelined loop
     if (tty) { fputs("\x1b[?25h", sink); fflush(sink); }         // lib.rs:568
     raw.leave();
     if (tty || verbose) fprintf(stderr, "Exiting.\n");           // lib.rs:570
     trt_free_host(bytes);
-    trt_destroy(ctx);
+    if (bytes2) trt_free_host(bytes2);
+    if (ctx) trt_destroy(ctx);
+    trt_multi_destroy(multi);
     trt_scene_free(scene);
     if (sink != stdout) fclose(sink);
     return status;
