@@ -208,6 +208,9 @@ class ShardedRenderer:
 
     def close(self):
         lib = self.pkg.api.lib()
+        # the tensor over the context's row-length buffer must go before the context frees that buffer
+        self.torch.cuda.synchronize(self.dev)
+        self.lens_local = self.lens_all = self.lens_host = self.block = self.gathered = None
         if self._host is not None:
             if self.world == 1:
                 lib.trt_free_host(self._host)

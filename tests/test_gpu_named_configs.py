@@ -155,7 +155,7 @@ def test_c4_full_scene_small_frame(pkg, O):
     sc = O.make_c4_scene()
     prims = O.flatten_scene(sc)
     assert len(prims) == 20484
-    w, h, spp = 28, 16, 256
+    w, h, spp = 24, 14, 256
     u = O.make_uniforms(sc, len(prims), O.C4_SEED, 0, width=w, height=h, spp=spp, max_depth=32)
     ref = render(prims, u)
     r = pkg.Renderer(w, h, conv=0)
@@ -172,10 +172,10 @@ def test_c4_full_scene_small_frame(pkg, O):
     kernel = rn.kernel_name()
     rn.close()
     assert "SrcTiled" in kernel
-    over, med = rel_over(gn, ref["pixels"])
-    print(f"\nC4 full scene {w}x{h} x {spp} spp, {kernel}: {over} of {w * h} pixels over 1e-4 (median {med:.2g})")
-    assert med < 5e-6
-    assert over <= w * h // 20                            # NEE live on every hit; the ill-conditioned shadow-ray end
+    # NEE is live on every hit here (4 lights x ~2 bounces x 64...256 samples = ~1000 light samples per pixel), and the
+    # shader's shadow ray ends within rounding of the light's own surface: ~1 in 1000 of them flips under
+    # ANY change of rounding, so the per-pixel count is judged against the contracted-reference yardstick
+    deep_path_bar(O, f"C4 full scene {w}x{h} x {spp} spp, {kernel}", gn, ref, prims, u)
 
 
 # ---- C5 -------------------------------------------------------------------------------------------------------------
