@@ -54,6 +54,12 @@ namespace trt {
 #ifndef TRT_NV_SLOTS
 #define TRT_NV_SLOTS 4
 #endif
+// TRT_V_ORDERED_LATE: light-sample sums join the owner's late sum in posting order (ordered_late_add) instead of by
+// `red.shared.add` in whatever order the batches and the hardware produce: conv 2 frames become run-to-run and
+// shard-union bit-identical.  0 = the round-1 behaviour (A/B).
+#ifndef TRT_V_ORDERED_LATE
+#define TRT_V_ORDERED_LATE 1
+#endif
 #define TRT_NV_RING 64           // queued hits per warp: at most 31 left over + 32 new ones per iteration
 #define TRT_NV_MAX_LIGHTS 16     // light mask bits in the entry's meta word
 
@@ -70,6 +76,32 @@ __device__ __forceinline__ void sts_f(unsigned a, float v) { asm volatile("st.sh
 __device__ __forceinline__ void sts_u(unsigned a, unsigned v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ void red_f(unsigned a, float v) { asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory"); }
 __device__ __forceinline__ void red_u(unsigned a, unsigned v) { asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+
+// Ordered addition of a batch of light-sample sums into the owners' late sums.  Several lanes of one queue pass may
+// hold entries of the SAME (owner, slot); `red.shared.add` would add them in an order the hardware chooses, and how
+// entries fall into batches depends on which pixels share a warp (dynamic hand-out, row shards).  Here the lowest lane
+// of every such group adds the group's values one after the other, in lane order = posting order, with plain loads and
+// stores (different groups touch different words): late = ((late + e1) + e2) ... whatever the batches were, so a conv 2
+// frame is run-to-run and shard-union bit-identical.  All 32 lanes call this; `active` lanes carry a value.
+__device__ __forceinline__ void ordered_late_add(bool active, unsigned key, unsigned addr, float3 v) {
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned peers = __match_any_sync(0xffffffffu, active ? key : (0x80000000u | lane));
+    const unsigned others = peers & ~(1u << lane);
+    if (!__any_sync(0xffffffffu, active && others != 0u)) {      // the common case: every owner appears once
+        if (active) { sts_f(addr, lds_f(addr) + v.x); sts_f(addr + 4u, lds_f(addr + 4u) + v.y); sts_f(addr + 8u, lds_f(addr + 8u) + v.z); }
+        return;
+    }
+    const bool leader = active && (peers & ((1u << lane) - 1u)) == 0u;
+    float3 t = leader ? f3(lds_f(addr) + v.x, lds_f(addr + 4u) + v.y, lds_f(addr + 8u) + v.z) : f3(0.0f, 0.0f, 0.0f);
+    unsigned rest = leader ? others : 0u;
+    const int n = (int)__reduce_max_sync(0xffffffffu, active ? (unsigned)__popc(peers) : 1u) - 1;
+    for (int i = 0; i < n; i++) {
+        const int src = rest ? __ffs(rest) - 1 : (int)lane;
+        const float x = __shfl_sync(0xffffffffu, v.x, src), y = __shfl_sync(0xffffffffu, v.y, src), z = __shfl_sync(0xffffffffu, v.z, src);
+        if (rest) { t.x += x; t.y += y; t.z += z; rest &= rest - 1u; }
+    }
+    if (leader) { sts_f(addr, t.x); sts_f(addr + 4u, t.y); sts_f(addr + 8u, t.z); }
+}
 
 // The sample of light k for a queued hit (shader.wgsl:350-429): sample point from the two draws (:352-389), the
 // two cosines (:403-404) and, when both are positive, the shadow ray (:394-399) and the clamped contribution
@@ -159,6 +191,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     float3 pixel_color = f3(0, 0, 0), sq_sum = f3(0, 0, 0);
     float3 att = f3(1, 1, 1), acc = f3(0, 0, 0);
     float3 ro = f3(0, 0, 0), rd = f3(0, 0, 1);   // this lane's closest-hit ray
+    float3 qsum = f3(0, 0, 0);                   // small scenes: the sum over the lights of the entry this lane is resolving
     const bool small = SHAPE::kFixed || (SRC::kSmall && c_small.ok);
 
 #if TRT_TAIL_DIAG
@@ -408,7 +441,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             if (sp_k < 0 && cnt > 0u) {
                 const unsigned m_active = __ballot_sync(0xffffffffu, mode == NM_ACTIVE);
                 const unsigned m_wait = __ballot_sync(0xffffffffu, mode == NM_WAIT);
-                if (cnt >= 32u || cnt + TRT_NV_WAIT_W * __popc(m_wait) >= 32u || !m_active) sp_k = 0;
+                if (cnt >= 32u || cnt + TRT_NV_WAIT_W * __popc(m_wait) >= 32u || !m_active) { sp_k = 0; qsum = f3(0, 0, 0); }
             }
             spass = sp_k >= 0;
             qn = cnt < 32u ? cnt : 32u;
@@ -453,8 +486,10 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         }
 
         if (spass) {                                              // shader.wgsl:402-431 for the queued samples
+            const bool lit = qvalid && t_hit < 0.0f && qneed;
+#if !TRT_V_ORDERED_LATE
             if (qvalid) {
-                if (t_hit < 0.0f && qneed) {
+                if (lit) {
                     const unsigned al = TRT_REC(qowner, kLate + 3u * qslot);
                     red_f(al, qc.x); red_f(al + 4u, qc.y); red_f(al + 8u, qc.z);
                 }
@@ -462,6 +497,26 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 else if (qrest) ring[DQ_RNG][qe] = __uint_as_float(qrng);
                 else red_u(TRT_REC(qowner, kRes), 1u);
             }
+#else
+            if (SRC::kTiled) {
+                // one ready ray per lane: added in FIFO order (= the owner's posting order, light by light)
+                __syncwarp();
+                ordered_late_add(lit, qowner << 2 | qslot, TRT_REC(qowner, kLate + 3u * qslot), qc);
+                if (qvalid) red_u(TRT_REC(qowner, kRes), 1u);
+            } else {
+                // the entry's lights are summed in light order in a register, the entry's sum joins the owner's late
+                // sum once, at its last light, in posting order
+                if (lit) qsum = V::add(qsum, qc);
+                if (qrest) {
+                    if (qvalid) ring[DQ_RNG][qe] = __uint_as_float(qrng);
+                } else {
+                    __syncwarp();
+                    ordered_late_add(qvalid && (qsum.x != 0.0f || qsum.y != 0.0f || qsum.z != 0.0f), qowner << 2 | qslot,
+                                     TRT_REC(qowner, kLate + 3u * qslot), qsum);
+                    if (qvalid) red_u(TRT_REC(qowner, kRes), 1u);
+                }
+            }
+#endif
             if (SRC::kTiled) {
                 rhead += qn;
             } else if (qrest) {
