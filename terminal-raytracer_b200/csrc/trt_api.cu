@@ -13,6 +13,7 @@
 #include "trt_kernels.cuh"
 #include "trt_persistent.cuh"
 #include "trt_wave.cuh"
+#include "trt_native.cuh"
 #include "trt_quantise.cuh"
 
 using namespace trt;
@@ -24,6 +25,40 @@ cudaError_t native_blend_launch(float4 *cur, const uint2 *batch, uint32_t n_batc
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
                                 cudaStream_t stream, uint32_t *launches, const char **kernel_name);
+}
+
+// The deferred-NEE machine (trt_native.cuh) in the strict conventions: conv 0 / 1, bit-exact against the oracle.
+// TRT_B200_STRICT=wave selects the round-1 strict kernel (trace_wave_kernel) for A/B runs.
+static cudaError_t strict_native_launch(int device, const SceneView &sv, const LightView &lv, const FrameParams &fp, int conv, int sm_count,
+                                        bool constant, cudaStream_t stream, uint32_t *launches, const char **name) {
+    cudaError_t e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    static bool carveout_set[64] = {};
+    if (device >= 0 && device < 64 && !carveout_set[device]) {
+        cudaFuncSetAttribute(trace_native_kernel<0, SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<1, SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<0, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<1, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        carveout_set[device] = true;
+    }
+    const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
+    const uint32_t want = (n_work + TRT_NV_THREADS - 1u) / TRT_NV_THREADS;
+    static const char *ctas_env = getenv("TRT_B200_STRICT_CTAS");
+    uint32_t ctas = fp.ctas_hint >= 1u && fp.ctas_hint < TRT_NV_STRICT_CTAS ? fp.ctas_hint : TRT_NV_STRICT_CTAS;
+    if (ctas_env && atoi(ctas_env) >= 1 && atoi(ctas_env) <= TRT_NV_STRICT_CTAS) ctas = (uint32_t)atoi(ctas_env);
+    const uint32_t cap = (uint32_t)sm_count * ctas;
+    const uint32_t blocks = want < cap ? want : cap;
+    if (constant) {
+        if (conv) trace_native_kernel<1, SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_native_kernel<0, SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        *name = "trace_native_kernel<CONV, SrcConst, ShapeAny> (strict)";
+    } else {
+        if (conv) trace_native_kernel<1, SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_native_kernel<0, SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        *name = "trace_native_kernel<CONV, SrcGlobal, ShapeAny> (strict)";
+    }
+    *launches += 1;
+    return cudaGetLastError();
 }
 
 struct trt_ctx {
@@ -565,14 +600,22 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
             // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)
             static const bool use_v1 = [] { const char *k = getenv("TRT_B200_KERNEL"); return k && !strcmp(k, "v1"); }();
+            static const bool use_wave = [] { const char *k = getenv("TRT_B200_STRICT"); return k && !strcmp(k, "wave"); }();
+            const bool deferred = !use_v1 && !use_wave && ctx->sv.n_lights <= TRT_NV_MAX_LIGHTS;
             if (e == cudaSuccess) {
-                if (use_v1 && !n_batch) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream, &ctx->launches);
+                if (deferred) {
+                    if (!n_batch) fp.cost = ctx->d_cost;
+                    e = strict_native_launch(ctx->device, ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, scene_fits_constant(ctx->sv),
+                                             ctx->stream, &ctx->launches, &ctx->kernel_name);
+                } else if (use_v1 && !n_batch) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream, &ctx->launches);
                 else e = wave_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, scene_fits_constant(ctx->sv),
                                            ctx->stream, &ctx->launches);
             }
             if (e != cudaSuccess) { ctx->err = std::string("trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
-            ctx->kernel_name = use_v1 && !n_batch ? "trace_persistent_kernel" : scene_fits_constant(ctx->sv) ? "trace_wave_kernel<CONV, SrcConst>"
-                                                                                                          : "trace_wave_kernel<CONV, SrcGlobal>";
+            ctx->cost_kernel = deferred;
+            if (!deferred)
+                ctx->kernel_name = use_v1 && !n_batch ? "trace_persistent_kernel" : scene_fits_constant(ctx->sv) ? "trace_wave_kernel<CONV, SrcConst>"
+                                                                                                              : "trace_wave_kernel<CONV, SrcGlobal>";
         }
         CK(cudaGetLastError());
     }

@@ -47,10 +47,10 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     const bool constant = scene_fits_constant(sv);
     static bool carveout_set = false;
     if (!carveout_set) {
-        cudaFuncSetAttribute(trace_native_kernel<SrcConst, ShapeCornell>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        cudaFuncSetAttribute(trace_native_kernel<SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        cudaFuncSetAttribute(trace_native_kernel<SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        cudaFuncSetAttribute(trace_native_kernel<SrcTiled, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<2, SrcConst, ShapeCornell>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<2, SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<2, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<2, SrcTiled, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         carveout_set = true;
     }
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
@@ -91,17 +91,17 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         name = jk->name.c_str();
     } else if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
         if (cornell) {
-            trace_native_kernel<SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            trace_native_kernel<2, SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
             name = "trace_native_kernel<SrcConst, ShapeCornell>";
         } else if (constant) {
-            trace_native_kernel<SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            trace_native_kernel<2, SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
             name = "trace_native_kernel<SrcConst, ShapeAny>";
         } else if (sv.n_tiles > 0 && !force_untiled) {
             const uint32_t tcap = (uint32_t)sm_count * SrcTiled::kCtasPerSm;
-            trace_native_kernel<SrcTiled, ShapeAny><<<want < tcap ? want : tcap, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            trace_native_kernel<2, SrcTiled, ShapeAny><<<want < tcap ? want : tcap, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
             name = "trace_native_kernel<SrcTiled, ShapeAny>";
         } else {
-            trace_native_kernel<SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            trace_native_kernel<2, SrcGlobal, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
             name = "trace_native_kernel<SrcGlobal, ShapeAny>";
         }
     } else {

@@ -66,7 +66,12 @@ namespace trt {
 enum { NM_ACTIVE = 0, NM_WAIT = 1, NM_NEED_PIXEL = 2, NM_DONE = 3 };
 // queue entry, 11 words: hit point, unit normal (facing the ray), colour x attenuation, random state before
 // the light loop (advanced light by light while the entry is being resolved), meta = owner thread | mask << 8
-enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ_META, DQ_FIELDS };
+enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ_META, DQ_FIELDS,
+       // strict builds (conv 0 / 1) keep colour and attenuation apart -- the shader multiplies (colour / pi) * emission
+       // and attenuation * (G * area) separately (:416-422), the product colour * attenuation would round differently --
+       // and carry the hit's own emission term (:455), which must join the sample's sum BEFORE its light samples:
+       // DQ_C* = colour, DQ_A* = attenuation, DQ_E* = emission * attenuation
+       DQ_AX = DQ_FIELDS, DQ_AY, DQ_AZ, DQ_EX, DQ_EY, DQ_EZ, DQ_FIELDS_STRICT };
 
 // Explicit shared-space accesses of the per-lane record (32-bit shared addresses: base + immediate, no generic
 // pointer kept in a register across the loop); "memory": ordered against the warp barriers around them.
@@ -106,13 +111,51 @@ __device__ __forceinline__ void ordered_late_add(bool active, unsigned key, unsi
 // The sample of light k for a queued hit (shader.wgsl:350-429): sample point from the two draws (:352-389), the
 // two cosines (:403-404) and, when both are positive, the shadow ray (:394-399) and the clamped contribution
 // (:408-429).  Returns whether the shadow ray is needed.
-template <class SHAPE, class TR>
-__device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, float3 C, float r1, float r2, float3 &qo, float3 &qd,
-                                           float &qt, float3 &qc) {
-    typedef M<2> V;
+template <int CONV, class SHAPE, class TR>
+__device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, float3 C, float3 A, float r1, float r2, float3 &qo,
+                                           float3 &qd, float &qt, float3 &qc) {
+    typedef M<CONV> V;
     const float4 a = tr.src.la(k);
     const float4 nl = tr.src.ln(k);
     const float4 em = tr.src.le(k);
+    if (CONV != 2) {
+        // as written, operation for operation (the sequence of trace_wave_kernel's light loop, trt_wave.cuh); C = the
+        // hit's colour, A = the attenuation at the hit
+        float3 light_point, light_normal;
+        if (SHAPE::light_is_sphere(k, __float_as_int(em.w))) {        // :352-369
+            const float cos_theta = 1.0f - 2.0f * r1;
+            const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+            float sp, cp;
+            sincos_turn<CONV>(r2, sp, cp);
+            const float3 local = f3(sin_theta * cp, sin_theta * sp, cos_theta);
+            light_point = V::axpy(xyz(a), local, a.w);
+            light_normal = local;
+        } else {                                                      // :370-389
+            const float sqrt_r1 = sqrtf(r1);
+            const float u = 1.0f - sqrt_r1;
+            const float v = r2 * sqrt_r1;
+            light_point = V::lin3(xyz(a), 1.0f - u - v, xyz(tr.src.lb(k)), u, xyz(tr.src.lc(k)), v);
+            light_normal = xyz(nl);
+        }
+        const float3 light_vec = V::sub(light_point, P);
+        const float d2 = V::dot(light_vec, light_vec);
+        const float sl = V::dot(light_normal, light_vec), ss = V::dot(N, light_vec);
+        // exact early out: a cosine that is certainly <= 0 (margin for the rounding of the normalisation)
+        if ((sl > 0.0f && sl * sl > 1e-11f * d2) || (ss < 0.0f && ss * ss > 1e-11f * d2)) return false;
+        const float light_distance = sqrtf(d2);
+        const float3 light_dir = V::divs(light_vec, light_distance);
+        const float cos_surface = fmaxf(0.0f, V::dot(N, light_dir));                                   // :403
+        const float cos_light = fmaxf(0.0f, V::dot(light_normal, V::scale(light_dir, -1.0f)));         // :404
+        if (!(cos_surface > 0.0f && cos_light > 0.0f)) return false;
+        const float geometric = (cos_surface * cos_light) / (light_distance * light_distance);         // :408-410
+        const float3 brdf = V::divs(C, TRT_PI_F);
+        const float3 c = V::mulv(V::mulv(brdf, xyz(em)), V::scale(A, geometric * nl.w));
+        qc = f3(fminf(c.x, 10.0f), fminf(c.y, 10.0f), fminf(c.z, 10.0f));
+        qo = V::axpy(P, N, 0.001f);                                                                    // :399
+        qd = light_dir;
+        qt = light_distance - 0.001f;
+        return true;
+    }
     float3 light_vec;
     float sl;
     if (SHAPE::light_is_sphere(k, __float_as_int(em.w))) {   // uniform sphere sampling :352-369
@@ -146,12 +189,19 @@ __device__ __forceinline__ bool nee_sample(TR &tr, int k, float3 P, float3 N, fl
 
 // the kernel body; the __global__ entry points are trace_native_kernel below and, for a scene-specialised build
 // compiled at run time, trt_jit_trace (trt_jit.cpp)
-template <class SRC, class SHAPE>
+// CONV 2: the production arithmetic.  CONV 0 / 1: the same machine in the strict conventions, BIT-EXACT against the
+// oracle: every term of a sample's radiance (the emission of a hit :455, its light samples :458-459) goes through the
+// sample's late sum in posting order = the shader's order of additions (ordered_late_add), nothing is added ahead of an
+// older pending term, and adaptive extra samples are closed whole like base samples (:596 adds complete values).
+template <int CONV, class SRC, class SHAPE>
 __device__ __forceinline__ void trace_native_body(const SceneView &sc, const LightView &lv, const FrameParams &fp) {
-    typedef M<2> V;
+    typedef M<CONV> V;
+    static_assert(CONV == 2 || !SRC::kTiled, "the tiled cooperative scan exists in the native convention only");
+    constexpr bool kStrict = CONV != 2;
+    constexpr int kFields = kStrict ? (int)DQ_FIELDS_STRICT : (int)DQ_FIELDS;
     Counters<false> cn;
-    Tracer<2, false, SRC> tr(sc, lv, fp, cn);
-    __shared__ float s_ring[TRT_NV_THREADS / 32][DQ_FIELDS][TRT_NV_RING];
+    Tracer<CONV, false, SRC> tr(sc, lv, fp, cn);
+    __shared__ float s_ring[TRT_NV_THREADS / 32][kFields][TRT_NV_RING];
     // Parking needs the queue to resolve a lane's entries in the order they were posted (the small-scene queue does:
     // an entry is resolved whole, at its last light).  The two-stage queue of SrcTiled resolves a light sample that
     // is not needed on the spot, ahead of older samples still in the ray FIFO: no parking there (one slot).
@@ -192,7 +242,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     float3 att = f3(1, 1, 1), acc = f3(0, 0, 0);
     float3 ro = f3(0, 0, 0), rd = f3(0, 0, 1);   // this lane's closest-hit ray
     float3 qsum = f3(0, 0, 0);                   // small scenes: the sum over the lights of the entry this lane is resolving
-    const bool small = SHAPE::kFixed || (SRC::kSmall && c_small.ok);
+    const bool small = !kStrict && (SHAPE::kFixed || (SRC::kSmall && c_small.ok));
 
 #if TRT_TAIL_DIAG
     // measurement build: when (0.5 ms bins from the first warp's start) this warp first found the work list empty
@@ -222,15 +272,15 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 const float3 a = f3(lds_f(ap) + lds_f(al), lds_f(ap + 4u) + lds_f(al + 4u), lds_f(ap + 8u) + lds_f(al + 8u));
                 sts_f(al, 0.0f); sts_f(al + 4u, 0.0f); sts_f(al + 8u, 0.0f);
                 pixel_color = V::add(pixel_color, a);
-                sq_sum = V::add(sq_sum, V::mulv(a, a));
+                if (!extra_phase) sq_sum = V::add(sq_sum, V::mulv(a, a));      // (strict: extra samples are parked too)
                 fin++;
             }
             // the sample that has just ended: an extra sample only adds to the pixel's sum (:596) and its light samples
             // may arrive until the pixel's last sample (all in slot 0); a base sample is closed if nothing is
             // outstanding, else parked if a slot is free for the next one; the last sample of a phase waits
-            const unsigned cs = extra_phase ? 0u : si & (kSlots - 1u);
+            const unsigned cs = (extra_phase && !kStrict) ? 0u : si & (kSlots - 1u);
             const bool last = si + 1u == target;
-            if (extra_phase && !last) {
+            if (!kStrict && extra_phase && !last) {
                 retire = closed = true;
             } else if (fin == si && r == pend) {
                 const unsigned al = TRT_REC(tid, kLate + 3u * cs);
@@ -392,7 +442,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     const float3 P = f3(ring[DQ_PX][ee], ring[DQ_PY][ee], ring[DQ_PZ][ee]);
                     const float3 N = f3(ring[DQ_NX][ee], ring[DQ_NY][ee], ring[DQ_NZ][ee]);
                     const float3 C = f3(ring[DQ_CX][ee], ring[DQ_CY][ee], ring[DQ_CZ][ee]);
-                    needed = nee_sample<SHAPE>(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
+                    needed = nee_sample<CONV, SHAPE>(tr, k, P, N, C, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                         __uint2float_rn(erng) * 2.3283064365386963e-10f, so, sd, st, scn);
                     if (!needed) red_u(TRT_REC(owner & 0xffu, kRes), 1u);
                 }
@@ -457,12 +507,12 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 }
                 const unsigned uni = __reduce_or_sync(0xffffffffu, lmask);
                 int k = sp_k;
-                while (!((uni >> k) & 1u)) {                      // lights no queued hit can see: only their draws
+                while (uni != 0u && !((uni >> k) & 1u)) {         // lights no queued hit can see: only their draws
                     qrng = pcg_hash(pcg_hash(qrng));
                     k++;
                 }
                 sp_k = k;
-                qrest = uni >> (k + 1);
+                qrest = uni ? uni >> (k + 1) : 0u;                // (strict: a batch may hold emission-only entries)
                 const uint32_t s1 = pcg_hash(qrng);               // the two draws of :350-351 / :371-372, in order
                 qrng = pcg_hash(s1);
                 qt = -1.0f;                                       // nothing to find unless the sample is needed
@@ -470,7 +520,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     const float3 P = f3(ring[DQ_PX][qe], ring[DQ_PY][qe], ring[DQ_PZ][qe]);
                     const float3 N = f3(ring[DQ_NX][qe], ring[DQ_NY][qe], ring[DQ_NZ][qe]);
                     const float3 C = f3(ring[DQ_CX][qe], ring[DQ_CY][qe], ring[DQ_CZ][qe]);
-                    qneed = nee_sample<SHAPE>(tr, k, P, N, C, __uint2float_rn(s1) * 2.3283064365386963e-10f,
+                    const float3 A = kStrict ? f3(ring[kStrict ? DQ_AX : 0][qe], ring[kStrict ? DQ_AY : 0][qe], ring[kStrict ? DQ_AZ : 0][qe]) : C;
+                    qneed = nee_sample<CONV, SHAPE>(tr, k, P, N, C, A, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                        __uint2float_rn(qrng) * 2.3283064365386963e-10f, qo, qd, qt, qc);
                 }
             }
@@ -482,7 +533,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
 #ifndef __CUDACC_RTC__
             else if (SRC::kTiled) t_hit = tr.scan_native_tiled(qo, qd, mode == NM_ACTIVE || spass ? qt : -1.0f, best, s_tile, spass);
 #endif
-            else t_hit = tr.scan_native(qo, qd, qt, best);
+            else t_hit = kStrict ? tr.scan_lean(qo, qd, qt, best) : tr.scan_native(qo, qd, qt, best);
         }
 
         if (spass) {                                              // shader.wgsl:402-431 for the queued samples
@@ -511,6 +562,13 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     if (qvalid) ring[DQ_RNG][qe] = __uint_as_float(qrng);
                 } else {
                     __syncwarp();
+                    if (kStrict) {                                // :455 before :459: the hit's own emission term first
+                        const float3 E = qvalid ? f3(ring[kStrict ? DQ_EX : 0][qe], ring[kStrict ? DQ_EY : 0][qe], ring[kStrict ? DQ_EZ : 0][qe])
+                                                : f3(0.0f, 0.0f, 0.0f);
+                        ordered_late_add(qvalid && (E.x != 0.0f || E.y != 0.0f || E.z != 0.0f), qowner << 2 | qslot,
+                                         TRT_REC(qowner, kLate + 3u * qslot), E);
+                        __syncwarp();
+                    }
                     ordered_late_add(qvalid && (qsum.x != 0.0f || qsum.y != 0.0f || qsum.z != 0.0f), qowner << 2 | qslot,
                                      TRT_REC(qowner, kLate + 3u * qslot), qsum);
                     if (qvalid) red_u(TRT_REC(qowner, kRes), 1u);
@@ -531,7 +589,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
 
         // ---- closest hit: miss -> sky, hit -> record (shader.wgsl:447-459, :280-290) ----------------------------
         bool path_end = false, hit = false;
-        float3 hp = f3(0, 0, 0), hn = f3(0, 1, 0);
+        float3 hp = f3(0, 0, 0), hn = f3(0, 1, 0), emis = f3(0, 0, 0);
         float4 mc = make_float4(0, 0, 0, 0);
         if (mode == NM_ACTIVE) {
             if (fp.max_depth == 0u) {
@@ -548,7 +606,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     hp = V::axpy(ro, rd, t_hit);
                     hn = tr.normal_at(best, __float_as_int(me.w), hp);
                     if (!(V::dot(rd, hn) < 0.0f)) hn = V::scale(hn, -1.0f);
-                    acc = V::vmad(acc, xyz(me), att);             // shader.wgsl:455
+                    if (kStrict) emis = V::mulv(xyz(me), att);    // :455, posted with the hit (order of additions)
+                    else acc = V::vmad(acc, xyz(me), att);        // shader.wgsl:455
                 }
             }
         }
@@ -576,16 +635,23 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 if (side > -1e-5f * (hp_mag + tr.src.lc(k).w)) lmask |= 1u << k;
             }
         }
-        const unsigned mp = __ballot_sync(0xffffffffu, lmask != 0u);
+        const bool post = lmask != 0u || (kStrict && (emis.x != 0.0f || emis.y != 0.0f || emis.z != 0.0f));
+        const unsigned mp = __ballot_sync(0xffffffffu, post);
         if (mp) {
-            if (lmask) {
+            if (post) {
                 const uint32_t e = (tail + __popc(mp & lt_mask)) & (TRT_NV_RING - 1u);
                 ring[DQ_PX][e] = hp.x; ring[DQ_PY][e] = hp.y; ring[DQ_PZ][e] = hp.z;
                 ring[DQ_NX][e] = hn.x; ring[DQ_NY][e] = hn.y; ring[DQ_NZ][e] = hn.z;
-                ring[DQ_CX][e] = mc.x * att.x; ring[DQ_CY][e] = mc.y * att.y; ring[DQ_CZ][e] = mc.z * att.z;
+                if (kStrict) {
+                    ring[DQ_CX][e] = mc.x; ring[DQ_CY][e] = mc.y; ring[DQ_CZ][e] = mc.z;
+                    ring[kStrict ? DQ_AX : 0][e] = att.x; ring[kStrict ? DQ_AY : 0][e] = att.y; ring[kStrict ? DQ_AZ : 0][e] = att.z;
+                    ring[kStrict ? DQ_EX : 0][e] = emis.x; ring[kStrict ? DQ_EY : 0][e] = emis.y; ring[kStrict ? DQ_EZ : 0][e] = emis.z;
+                } else {
+                    ring[DQ_CX][e] = mc.x * att.x; ring[DQ_CY][e] = mc.y * att.y; ring[DQ_CZ][e] = mc.z * att.z;
+                }
                 ring[DQ_RNG][e] = __uint_as_float(rng0);
                 // meta: owner thread | light mask << 8 | slot of the sample << 24 (extra samples: slot 0)
-                ring[DQ_META][e] = __uint_as_float(tid | (lmask << 8) | ((kSlots > 1u && !extra_phase ? si & (kSlots - 1u) : 0u) << 24));
+                ring[DQ_META][e] = __uint_as_float(tid | (lmask << 8) | ((kSlots > 1u && (kStrict || !extra_phase) ? si & (kSlots - 1u) : 0u) << 24));
                 pend += SRC::kTiled ? (uint32_t)__popc(lmask) : 1u;      // units to resolve: light samples / the entry
             }
             tail += __popc(mp);
@@ -596,7 +662,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         if (hit) {
             float3 s;
             if (mc.w > rnd(rng)) s = V::reflect(rd, hn);
-            else s = tr.cosine_hemisphere_unit(rng, hn);
+            else s = kStrict ? tr.cosine_hemisphere(rng, hn) : tr.cosine_hemisphere_unit(rng, hn);
             att = V::mulv(att, xyz(mc));
             ro = V::axpy(hp, s, 0.001f);
             rd = s;
@@ -622,10 +688,13 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
 #undef TRT_REC
 }
 
-template <class SRC, class SHAPE>
-__global__ void __launch_bounds__(TRT_NV_THREADS, SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
+#ifndef TRT_NV_STRICT_CTAS
+#define TRT_NV_STRICT_CTAS 6     // strict builds: 80 registers (IEEE division / square-root sequences), 34 KB of shared memory
+#endif
+template <int CONV, class SRC, class SHAPE>
+__global__ void __launch_bounds__(TRT_NV_THREADS, CONV != 2 ? TRT_NV_STRICT_CTAS : SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
 trace_native_kernel(SceneView sc, LightView lv, FrameParams fp) {
-    trace_native_body<SRC, SHAPE>(sc, lv, fp);
+    trace_native_body<CONV, SRC, SHAPE>(sc, lv, fp);
 }
 
 }  // namespace trt

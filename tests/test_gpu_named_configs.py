@@ -51,7 +51,7 @@ def deep_path_bar(O, tag, got, ref, prims, u_np, idx=None):
     """north_star's bars for a frame of deep paths (depth 32): the 1e-4 per-pixel bar is stated for single-bounce
     radiance; a depth-32 path through two mirror spheres amplifies ANY change of rounding, so whole samples take other
     branches.  Bars: (i) RMSE against the strict frame below half the Monte-Carlo noise floor (seed-to-seed RMSE of the
-    checker itself); (ii) pixels over 1e-4 at most 3x the YARDSTICK + 1 % of the pixels, the yardstick being the
+    checker itself) or twice the yardstick's own RMSE; (ii) pixels over 1e-4 at most 3x the YARDSTICK + 1 % of the pixels, the yardstick being the
     reference's own shader text compiled with FMA contraction allowed (oracle/_ref/libref_fma.so: another legal
     rounding of the reference) against its strict compilation; (iii) the median pixel within 2e-6."""
     over, med = rel_over(got, ref["pixels"])
@@ -61,14 +61,18 @@ def deep_path_bar(O, tag, got, ref, prims, u_np, idx=None):
     render = O.ref_render if O.ref_available() else O.render
     noise = rmse(render(prims, u2, **kw)["pixels"], ref["pixels"])
     r = rmse(got, ref["pixels"])
-    yard = None
+    yard, yard_rmse = None, 0.0
     if O.ref_available():
-        yard, _ = rel_over(O.ref_render(prims, u_np, fma=True, **kw)["pixels"], ref["pixels"])
+        fma = O.ref_render(prims, u_np, fma=True, **kw)["pixels"]
+        yard, _ = rel_over(fma, ref["pixels"])
+        yard_rmse = rmse(fma, ref["pixels"])
     n = len(got)
     print(f"\n{tag}: {over} of {n} pixels over 1e-4 (median {med:.2g}); RMSE {r:.4g} = {r / noise:.3f} of the noise floor {noise:.4g}; "
-          f"yardstick (reference text, contracted): {yard} pixels")
+          f"yardstick (reference text, contracted): {yard} pixels, RMSE {yard_rmse:.4g}")
     assert med < 2e-6
-    assert r <= 0.5 * noise
+    # (a frame that is mostly sky has a tiny noise floor while ONE flipped light sample moves a pixel by up to 10 / spp:
+    # the contracted reference shows the same outliers, hence the second term)
+    assert r <= max(0.5 * noise, 2.0 * yard_rmse)
     assert over <= (3 * yard if yard is not None else n // 8) + n // 100
     return over
 

@@ -12,7 +12,7 @@ HDRS = ["trt_device.cuh", "trt_trace.cuh", "trt_native.cuh"]
 def compile_shape(shape="ShapeFixed<3, 6, 2, 0xa05u, 2, 0x0u, 0x4deu>", extra=()):
     src = ('#include "trt_native.cuh"\nnamespace trt {\ntypedef %s JitShape;\nextern "C" __global__ void '
            '__launch_bounds__(TRT_NV_THREADS, TRT_NV_CTAS_PER_SM)\ntrt_jit_trace(SceneView sc, LightView lv, FrameParams fp) '
-           '{ trace_native_body<SrcConst, JitShape>(sc, lv, fp); }\n}\n' % shape).encode()
+           '{ trace_native_body<2, SrcConst, JitShape>(sc, lv, fp); }\n}\n' % shape).encode()
     texts = [open(os.path.join(CSRC, h), "rb").read() for h in HDRS]
     err, prog = nvrtc.nvrtcCreateProgram(src, b"trt_jit.cu", len(HDRS), texts, [h.encode() for h in HDRS])
     assert err == nvrtc.nvrtcResult.NVRTC_SUCCESS, err
