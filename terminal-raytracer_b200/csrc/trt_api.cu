@@ -111,6 +111,10 @@ struct trt_ctx {
     uint32_t last_q_blocks = 0;
     bool have_stream = false;
     int last_mode = TRT_MODE_NONE;
+    // one-pass quantiser: tile states of the look-back (+ the ticket in front), row starts of the last stream
+    unsigned long long *d_tile_state = nullptr;
+    uint64_t *d_row_start = nullptr;
+    bool fused_rows = false;           // d_row_start describes the last quantised stream
 
     // row-addressed stream: byte length of every row of the last quantised frame (local row order)
     uint32_t *d_row_len = nullptr;
@@ -182,7 +186,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_tiles, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
                     ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
                     ctx->d_cost, ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream,
-                    ctx->d_row_len, ctx->d_row_src_g, ctx->d_stream2};
+                    ctx->d_row_len, ctx->d_row_src_g, ctx->d_stream2, ctx->d_tile_state, ctx->d_row_start};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
     if (ctx->h_row_len) cudaFreeHost(ctx->h_row_len);
@@ -249,6 +253,8 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
         const size_t nb = (ctx->max_pixels + TRT_Q_BLOCK - 1) / TRT_Q_BLOCK;
         CK(cudaMalloc(&ctx->d_block_len, nb * sizeof(uint32_t)));
         CK(cudaMalloc(&ctx->d_block_off, (nb + 1) * sizeof(uint64_t)));
+        CK(cudaMalloc(&ctx->d_tile_state, ((ctx->max_pixels + TRT_QF_TILE - 1) / TRT_QF_TILE + 2) * sizeof(unsigned long long)));
+        CK(cudaMalloc(&ctx->d_row_start, ((size_t)cfg->max_height + 1) * sizeof(uint64_t)));
         ctx->stream_cap = ctx->max_pixels * 26 + (size_t)cfg->max_height * 2 + 64;
         CK(cudaMalloc(&ctx->d_stream, ctx->stream_cap));
         CK(cudaMallocHost(&ctx->h_len, 64));
@@ -655,7 +661,21 @@ static int launch_quantise(trt_ctx *ctx, const float4 *src, const uint64_t *row_
     q.packed = ctx->d_packed; q.block_len = ctx->d_block_len; q.block_off = ctx->d_block_off;
     q.n_blocks = (uint32_t)((n + TRT_Q_BLOCK - 1) / TRT_Q_BLOCK);
     q.out = d_out ? d_out : ctx->d_stream; q.out_cap = d_out ? out_cap : ctx->stream_cap;
-    if (q.n_blocks) {
+    // one pass (decoupled look-back) unless TRT_B200_QUANT=3pass asks for the round-1 three-launch form (A/B)
+    static const bool three_pass = [] { const char *k = getenv("TRT_B200_QUANT"); return k && !strcmp(k, "3pass"); }();
+    ctx->fused_rows = false;
+    if (q.n_blocks && !three_pass) {
+        q.n_tiles = (uint32_t)((n + TRT_QF_TILE - 1) / TRT_QF_TILE);
+        q.ticket = (unsigned int *)ctx->d_tile_state;              // word 0: the ticket; states from word 1
+        q.tile_state = ctx->d_tile_state + 1;
+        q.row_start = d_out ? nullptr : ctx->d_row_start;
+        q.total = (uint64_t *)(ctx->d_block_off + q.n_blocks);
+        CK(cudaMemsetAsync(ctx->d_tile_state, 0, ((size_t)q.n_tiles + 1) * sizeof(unsigned long long), ctx->stream));
+        quant_fused_kernel<<<q.n_tiles, TRT_Q_BLOCK, 0, ctx->stream>>>(q);
+        ctx->launches += 1;
+        CK(cudaGetLastError());
+        ctx->fused_rows = d_out == nullptr;
+    } else if (q.n_blocks) {
         quant_pack_kernel<<<q.n_blocks, TRT_Q_BLOCK, 0, ctx->stream>>>(q);
         quant_scan_kernel<<<1, 1024, 0, ctx->stream>>>(q);
         quant_emit_kernel<<<q.n_blocks, TRT_Q_BLOCK, 0, ctx->stream>>>(q);
@@ -733,7 +753,8 @@ extern "C" int trt_quantise_rows_async(trt_ctx *ctx, int mode) {
     if (rc) return rc;
     const uint32_t rows = (uint32_t)ctx->rows.size();
     if (rows) {
-        quant_row_len_kernel<<<(rows + 7u) / 8u, 256, 0, ctx->stream>>>(ctx->d_packed, ctx->last_u.width, rows, mode, ctx->d_row_len);
+        if (ctx->fused_rows) quant_row_len_from_starts_kernel<<<(rows + 255u) / 256u, 256, 0, ctx->stream>>>(ctx->d_row_start, rows, ctx->d_row_len);
+        else quant_row_len_kernel<<<(rows + 7u) / 8u, 256, 0, ctx->stream>>>(ctx->d_packed, ctx->last_u.width, rows, mode, ctx->d_row_len);
         ctx->launches += 1;
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(ctx->h_row_len, ctx->d_row_len, rows * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));

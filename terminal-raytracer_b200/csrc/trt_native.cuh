@@ -70,7 +70,7 @@ enum { DQ_PX, DQ_PY, DQ_PZ, DQ_NX, DQ_NY, DQ_NZ, DQ_CX, DQ_CY, DQ_CZ, DQ_RNG, DQ
        // strict builds (conv 0 / 1) keep colour and attenuation apart -- the shader multiplies (colour / pi) * emission
        // and attenuation * (G * area) separately (:416-422), the product colour * attenuation would round differently --
        // and carry the hit's own emission term (:455), which must join the sample's sum BEFORE its light samples:
-       // DQ_C* = colour, DQ_A* = attenuation, DQ_E* = emission * attenuation
+       // DQ_C* = colour, DQ_A* = attenuation, DQ_E* = the hit's emission (or the sky colour of a path that left the scene)
        DQ_AX = DQ_FIELDS, DQ_AY, DQ_AZ, DQ_EX, DQ_EY, DQ_EZ, DQ_FIELDS_STRICT };
 
 // Explicit shared-space accesses of the per-lane record (32-bit shared addresses: base + immediate, no generic
@@ -88,22 +88,43 @@ __device__ __forceinline__ void red_u(unsigned a, unsigned v) { asm volatile("re
 // of every such group adds the group's values one after the other, in lane order = posting order, with plain loads and
 // stores (different groups touch different words): late = ((late + e1) + e2) ... whatever the batches were, so a conv 2
 // frame is run-to-run and shard-union bit-identical.  All 32 lanes call this; `active` lanes carry a value.
-__device__ __forceinline__ void ordered_late_add(bool active, unsigned key, unsigned addr, float3 v) {
+// CONV != 2 (strict builds): every lane first adds its hit's emission term the way the shader does -- acc = acc +
+// emission * attenuation, :455, one fused multiply-add in conv 1 -- and then the sum of its light samples (:459);
+// a zero emission changes nothing.  (A path that leaves the scene posts its sky term the same way, :450.)
+template <int CONV>
+__device__ __forceinline__ void ordered_late_add(bool active, unsigned key, unsigned addr, float3 e, float3 a, float3 v) {
+    typedef M<CONV> V;
+    constexpr bool PAIR = CONV != 2;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned peers = __match_any_sync(0xffffffffu, active ? key : (0x80000000u | lane));
     const unsigned others = peers & ~(1u << lane);
     if (!__any_sync(0xffffffffu, active && others != 0u)) {      // the common case: every owner appears once
-        if (active) { sts_f(addr, lds_f(addr) + v.x); sts_f(addr + 4u, lds_f(addr + 4u) + v.y); sts_f(addr + 8u, lds_f(addr + 8u) + v.z); }
+        if (active) {
+            float3 t = f3(lds_f(addr), lds_f(addr + 4u), lds_f(addr + 8u));
+            if (PAIR) t = V::vmad(t, e, a);
+            t = V::add(t, v);
+            sts_f(addr, t.x); sts_f(addr + 4u, t.y); sts_f(addr + 8u, t.z);
+        }
         return;
     }
     const bool leader = active && (peers & ((1u << lane) - 1u)) == 0u;
-    float3 t = leader ? f3(lds_f(addr) + v.x, lds_f(addr + 4u) + v.y, lds_f(addr + 8u) + v.z) : f3(0.0f, 0.0f, 0.0f);
+    float3 t = f3(0.0f, 0.0f, 0.0f);
+    if (leader) {
+        t = f3(lds_f(addr), lds_f(addr + 4u), lds_f(addr + 8u));
+        if (PAIR) t = V::vmad(t, e, a);
+        t = V::add(t, v);
+    }
     unsigned rest = leader ? others : 0u;
     const int n = (int)__reduce_max_sync(0xffffffffu, active ? (unsigned)__popc(peers) : 1u) - 1;
     for (int i = 0; i < n; i++) {
         const int src = rest ? __ffs(rest) - 1 : (int)lane;
-        const float x = __shfl_sync(0xffffffffu, v.x, src), y = __shfl_sync(0xffffffffu, v.y, src), z = __shfl_sync(0xffffffffu, v.z, src);
-        if (rest) { t.x += x; t.y += y; t.z += z; rest &= rest - 1u; }
+        if (PAIR) {
+            const float3 pe = f3(__shfl_sync(0xffffffffu, e.x, src), __shfl_sync(0xffffffffu, e.y, src), __shfl_sync(0xffffffffu, e.z, src));
+            const float3 pa = f3(__shfl_sync(0xffffffffu, a.x, src), __shfl_sync(0xffffffffu, a.y, src), __shfl_sync(0xffffffffu, a.z, src));
+            if (rest) t = V::vmad(t, pe, pa);
+        }
+        const float3 pv = f3(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src));
+        if (rest) { t = V::add(t, pv); rest &= rest - 1u; }
     }
     if (leader) { sts_f(addr, t.x); sts_f(addr + 4u, t.y); sts_f(addr + 8u, t.z); }
 }
@@ -552,7 +573,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             if (SRC::kTiled) {
                 // one ready ray per lane: added in FIFO order (= the owner's posting order, light by light)
                 __syncwarp();
-                ordered_late_add(lit, qowner << 2 | qslot, TRT_REC(qowner, kLate + 3u * qslot), qc);
+                ordered_late_add<2>(lit, qowner << 2 | qslot, TRT_REC(qowner, kLate + 3u * qslot), qc, qc, qc);
                 if (qvalid) red_u(TRT_REC(qowner, kRes), 1u);
             } else {
                 // the entry's lights are summed in light order in a register, the entry's sum joins the owner's late
@@ -562,15 +583,13 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     if (qvalid) ring[DQ_RNG][qe] = __uint_as_float(qrng);
                 } else {
                     __syncwarp();
-                    if (kStrict) {                                // :455 before :459: the hit's own emission term first
-                        const float3 E = qvalid ? f3(ring[kStrict ? DQ_EX : 0][qe], ring[kStrict ? DQ_EY : 0][qe], ring[kStrict ? DQ_EZ : 0][qe])
-                                                : f3(0.0f, 0.0f, 0.0f);
-                        ordered_late_add(qvalid && (E.x != 0.0f || E.y != 0.0f || E.z != 0.0f), qowner << 2 | qslot,
-                                         TRT_REC(qowner, kLate + 3u * qslot), E);
-                        __syncwarp();
-                    }
-                    ordered_late_add(qvalid && (qsum.x != 0.0f || qsum.y != 0.0f || qsum.z != 0.0f), qowner << 2 | qslot,
-                                     TRT_REC(qowner, kLate + 3u * qslot), qsum);
+                    // strict: the hit's own emission term (:455) first, then its light samples (:459), entry by entry
+                    const float3 E = kStrict && qvalid ? f3(ring[kStrict ? DQ_EX : 0][qe], ring[kStrict ? DQ_EY : 0][qe], ring[kStrict ? DQ_EZ : 0][qe])
+                                                       : f3(0.0f, 0.0f, 0.0f);
+                    const float3 EA = kStrict && qvalid ? f3(ring[kStrict ? DQ_AX : 0][qe], ring[kStrict ? DQ_AY : 0][qe], ring[kStrict ? DQ_AZ : 0][qe])
+                                                        : f3(0.0f, 0.0f, 0.0f);
+                    const bool any = qsum.x != 0.0f || qsum.y != 0.0f || qsum.z != 0.0f || E.x != 0.0f || E.y != 0.0f || E.z != 0.0f;
+                    ordered_late_add<CONV>(qvalid && any, qowner << 2 | qslot, TRT_REC(qowner, kLate + 3u * qslot), E, EA, qsum);
                     if (qvalid) red_u(TRT_REC(qowner, kRes), 1u);
                 }
             }
@@ -597,7 +616,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
             } else {
                 tr.n_bounces++;
                 if (t_hit < 0.0f) {
-                    acc = V::vmad(acc, tr.sky(rd), att);
+                    if (kStrict) emis = tr.sky(rd);               // :450, posted like an emission term (order of additions)
+                    else acc = V::vmad(acc, tr.sky(rd), att);
                     path_end = true;
                 } else {
                     hit = true;
@@ -606,7 +626,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     hp = V::axpy(ro, rd, t_hit);
                     hn = tr.normal_at(best, __float_as_int(me.w), hp);
                     if (!(V::dot(rd, hn) < 0.0f)) hn = V::scale(hn, -1.0f);
-                    if (kStrict) emis = V::mulv(xyz(me), att);    // :455, posted with the hit (order of additions)
+                    if (kStrict) emis = xyz(me);                  // :455, posted with the hit (order of additions)
                     else acc = V::vmad(acc, xyz(me), att);        // shader.wgsl:455
                 }
             }

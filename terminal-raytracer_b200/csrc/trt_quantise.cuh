@@ -29,6 +29,12 @@ struct QuantParams {
     uint32_t n_blocks;
     uint8_t *out;
     uint64_t out_cap;
+    // one-pass form (quant_fused_kernel)
+    unsigned int *ticket;          // next tile to hand out (zeroed before the launch)
+    unsigned long long *tile_state;// per tile: flag << 62 | byte count (aggregate of the tile, or inclusive prefix); zeroed
+    uint64_t *row_start;           // rows + 1: stream offset of every row's first byte, [rows] = stream length
+    uint64_t *total;               // stream length (device word the host copies)
+    uint32_t n_tiles;
 };
 
 // lib.rs:521 -- 68 glyphs
@@ -187,6 +193,111 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_emit_kernel(QuantParams q) 
     uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
     for (uint32_t k = threadIdx.x; k < body / 16u; k += TRT_Q_BLOCK) d4[k] = s4[k];
     for (uint32_t k = head + body + threadIdx.x; k < total; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
+}
+
+// ---- one pass: quantise + scan + emit fused (decoupled look-back) ------------------------------------------------
+// The three-launch form reads the frame (16 B/px), writes and re-reads 4 B/px of packed colours twice and 12 B per 256
+// pixels of scan state.  Here one CTA takes a tile of TRT_QF_TILE pixels (dynamic tile index, so every predecessor has
+// started), quantises it in registers, publishes the tile's byte count, obtains its stream offset by looking back over
+// its predecessors' published counts (a warp reads 32 of them at a time), stages the text in shared memory and writes
+// it with 16-byte stores: HBM traffic = 16 B/px in + the stream out, the algorithmic minimum.  The thread that owns the
+// first pixel of a row also records where that row starts (row-addressed streams need every row's length).
+#define TRT_QF_PER_THREAD 4
+#define TRT_QF_TILE (TRT_Q_BLOCK * TRT_QF_PER_THREAD)
+#define TRT_QF_STAGE (TRT_QF_TILE * 28 + 32)
+#define TRT_QF_FLAG_AGG (1ull << 62)
+#define TRT_QF_FLAG_PFX (2ull << 62)
+#define TRT_QF_VALUE (~(3ull << 62))
+
+__device__ __forceinline__ unsigned long long ld_acquire_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q) {
+    __shared__ __align__(16) uint8_t stage[TRT_QF_STAGE];
+    __shared__ unsigned int s_tile;
+    __shared__ unsigned long long s_base;
+    if (threadIdx.x == 0) s_tile = atomicAdd(q.ticket, 1u);
+    __syncthreads();
+    const unsigned int tile = s_tile;
+    const uint64_t n = (uint64_t)q.width * q.height;
+    const uint64_t i0 = (uint64_t)tile * TRT_QF_TILE + (uint64_t)threadIdx.x * TRT_QF_PER_THREAD;
+    uint32_t pk[TRT_QF_PER_THREAD], len[TRT_QF_PER_THREAD], mine = 0;
+    uint32_t y = (uint32_t)(i0 / q.width), x = (uint32_t)(i0 - (uint64_t)y * q.width);
+#pragma unroll
+    for (int j = 0; j < TRT_QF_PER_THREAD; j++) {
+        pk[j] = 0; len[j] = 0;
+        if (i0 + j < n) {
+            const uint64_t src = q.row_src ? q.row_src[y] + x : i0 + j;
+            pk[j] = quantise_pixel(__ldg(&q.src[src]), q.mode);
+            len[j] = pixel_len(pk[j], q.mode, x == q.width - 1u) | (x == 0u ? 0x80000000u : 0u);   // bit 31: first pixel of row y_j
+            mine += len[j] & 0xffu;
+            if (++x == q.width) { x = 0; y++; }
+        }
+    }
+    uint32_t total;
+    const uint32_t local = block_exclusive_scan(mine, total);
+    // ---- the tile's offset in the stream: publish the aggregate, look back (warp 0) --------------------------------
+    if (threadIdx.x < 32u) {
+        const unsigned lane = threadIdx.x;
+        if (lane == 0) st_release_u64(&q.tile_state[tile], (tile == 0 ? TRT_QF_FLAG_PFX : TRT_QF_FLAG_AGG) | total);
+        unsigned long long excl = 0;
+        int pred = (int)tile - 1;
+        while (pred >= 0) {
+            const int t = pred - (int)lane;
+            unsigned long long st = TRT_QF_FLAG_PFX;                       // before the first tile: prefix 0
+            if (t >= 0) {
+                do { st = ld_acquire_u64(&q.tile_state[t]); } while ((st >> 62) == 0ull);
+            }
+            const unsigned has_pfx = __ballot_sync(0xffffffffu, (st >> 62) == 2ull);
+            const int first = has_pfx ? __ffs(has_pfx) - 1 : 31;           // nearest predecessor that knows its prefix
+            unsigned long long v = (int)lane <= first ? (st & TRT_QF_VALUE) : 0ull;
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            excl += v;
+            if (has_pfx) break;
+            pred -= 32;
+        }
+        if (lane == 0) {
+            if (tile != 0) st_release_u64(&q.tile_state[tile], TRT_QF_FLAG_PFX | (excl + total));
+            s_base = excl;
+            if (tile == q.n_tiles - 1u) { *q.total = excl + total; if (q.row_start) q.row_start[q.height] = excl + total; }
+        }
+    }
+    __syncthreads();
+    const uint64_t off = s_base;
+    if (off + total > q.out_cap) return;                 // caller checks the length first
+    const uint32_t pad = (uint32_t)((uintptr_t)(q.out + off) & 15u);
+    uint32_t pos = local;
+    uint32_t yy = (uint32_t)(i0 / q.width), xx = (uint32_t)(i0 - (uint64_t)yy * q.width);
+#pragma unroll
+    for (int j = 0; j < TRT_QF_PER_THREAD; j++) {
+        if (i0 + j < n) {
+            if ((len[j] >> 31) && q.row_start) q.row_start[yy] = off + pos;
+            put_pixel(stage + pad + pos, pk[j], q.mode, xx == q.width - 1u);
+            pos += len[j] & 0xffu;
+            if (++xx == q.width) { xx = 0; yy++; }
+        }
+    }
+    __syncthreads();
+    uint8_t *dst = q.out + off;                          // dst + k  <->  stage[pad + k]
+    const uint32_t head = min(total, (16u - pad) & 15u); // bytes before the first 16-byte boundary
+    const uint32_t body = (total - head) & ~15u;
+    for (uint32_t k = threadIdx.x; k < head; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(stage + pad + head);
+    uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
+    for (uint32_t k = threadIdx.x; k < body / 16u; k += TRT_Q_BLOCK) d4[k] = s4[k];
+    for (uint32_t k = head + body + threadIdx.x; k < total; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
+}
+
+// row lengths from the row starts the fused kernel recorded
+__global__ void quant_row_len_from_starts_kernel(const uint64_t *row_start, uint32_t rows, uint32_t *row_len) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < rows) row_len[r] = (uint32_t)(row_start[r + 1] - row_start[r]);
 }
 
 // Byte length of every row of the last quantised frame (one warp per row): what a shard publishes so that the rows of
