@@ -459,7 +459,9 @@ def ours(args):
     # ---- parity of the named configuration itself (strided subset against the CPU build of the reference's shader) ----
     parity = None
     if world == 1 and not args.no_parity:
-        parity = parity_block(pkg, O, wl, prims_np, scene, cam, local, args.conv, args.parity_pixels, sr.r)
+        # (a C4 pixel costs the CPU ~10^4 times a Cornell pixel: 20 484 tests per scan, five scans per bounce)
+        n_par = min(args.parity_pixels, 160) if wl["name"] == "c4" else args.parity_pixels
+        parity = parity_block(pkg, O, wl, prims_np, scene, cam, local, args.conv, n_par, sr.r)
 
     # ---- the same frame in the strict convention (conv 0: bit-exact against the oracle), for comparison ----
     strict = None

@@ -30,7 +30,7 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
 // The deferred-NEE machine (trt_native.cuh) in the strict conventions: conv 0 / 1, bit-exact against the oracle.
 // TRT_B200_STRICT=wave selects the round-1 strict kernel (trace_wave_kernel) for A/B runs.
 static cudaError_t strict_native_launch(int device, const SceneView &sv, const LightView &lv, const FrameParams &fp, int conv, int sm_count,
-                                        bool constant, cudaStream_t stream, uint32_t *launches, const char **name) {
+                                        bool constant, bool cornell, cudaStream_t stream, uint32_t *launches, const char **name) {
     cudaError_t e = cudaMemsetAsync(fp.work_counter, 0, sizeof(unsigned int), stream);
     if (e != cudaSuccess) return e;
     static bool carveout_set[64] = {};
@@ -39,6 +39,8 @@ static cudaError_t strict_native_launch(int device, const SceneView &sv, const L
         cudaFuncSetAttribute(trace_native_kernel<1, SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<0, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<1, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<0, SrcConst, ShapeCornellStrict>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_native_kernel<1, SrcConst, ShapeCornellStrict>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         carveout_set[device] = true;
     }
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
@@ -48,7 +50,12 @@ static cudaError_t strict_native_launch(int device, const SceneView &sv, const L
     if (ctas_env && atoi(ctas_env) >= 1 && atoi(ctas_env) <= TRT_NV_STRICT_CTAS) ctas = (uint32_t)atoi(ctas_env);
     const uint32_t cap = (uint32_t)sm_count * ctas;
     const uint32_t blocks = want < cap ? want : cap;
-    if (constant) {
+    if (constant && cornell) {
+        // the reference's default scene layout: the strict scan with its run list known to the compiler
+        if (conv) trace_native_kernel<1, SrcConst, ShapeCornellStrict><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_native_kernel<0, SrcConst, ShapeCornellStrict><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        *name = "trace_native_kernel<CONV, SrcConst, ShapeCornell> (strict)";
+    } else if (constant) {
         if (conv) trace_native_kernel<1, SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
         else trace_native_kernel<0, SrcConst, ShapeAny><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
         *name = "trace_native_kernel<CONV, SrcConst, ShapeAny> (strict)";
@@ -84,6 +91,7 @@ struct trt_ctx {
     LightView lv{};
     SmallScene small{};                // canonical small-scene mirror for the conv 2 scan (host copy)
     bool have_scene = false;
+    bool cornell_runs = false;         // the scene has the default Cornell layout incl. its run list (RunsCornell)
     uint64_t scene_serial = 0;
 
     // frame buffers (lib.rs:269-319: accumulation, output(pixels), variance; staging -> byte stream)
@@ -434,6 +442,21 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     ctx->sv.type = ctx->d_type; ctx->sv.runs = ctx->d_runs; ctx->sv.lights = ctx->d_lights;
     ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;
     ctx->sv.tiles = ctx->d_tiles; ctx->sv.n_tiles = (int)tiles.size();
+    {   // default Cornell layout (ShapeCornell) with exactly the run list RunsCornell: the strict specialised kernel
+        bool c = ctx->small.ok && ctx->small.n_sph == ShapeCornell::NS && ctx->small.n_pl == ShapeCornell::NP &&
+                 ctx->small.n_tri == ShapeCornell::NT && n_lights == (uint32_t)ShapeCornell::NL && ctx->small.n_light_spheres == 0 &&
+                 (int)runs.size() == RunsCornell::kCount;
+        for (int j = 0; c && j < ShapeCornell::NP; j++) {
+            int kind;
+            memcpy(&kind, &ctx->small.pl_p[j].w, 4);
+            c = kind == ShapeCornell::kind(j);
+        }
+        for (int r = 0; c && r < RunsCornell::kCount; r++) {
+            const int4 e = RunsCornell::run(r);
+            c = runs[r].x == e.x && runs[r].y == e.y && runs[r].z == e.z;
+        }
+        ctx->cornell_runs = c;
+    }
     ctx->lv.la = rp.la; ctx->lv.lb = rp.lb; ctx->lv.lc = rp.lc; ctx->lv.ln = rp.ln; ctx->lv.le = rp.le;
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->have_scene = true;
@@ -611,8 +634,9 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
             if (e == cudaSuccess) {
                 if (deferred) {
                     if (!n_batch) fp.cost = ctx->d_cost;
+                    static const bool generic = [] { const char *k = getenv("TRT_B200_STRICT"); return k && !strcmp(k, "generic"); }();
                     e = strict_native_launch(ctx->device, ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, scene_fits_constant(ctx->sv),
-                                             ctx->stream, &ctx->launches, &ctx->kernel_name);
+                                             ctx->cornell_runs && !generic, ctx->stream, &ctx->launches, &ctx->kernel_name);
                 } else if (use_v1 && !n_batch) e = persistent_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, ctx->stream, &ctx->launches);
                 else e = wave_trace_launch(ctx->sv, ctx->lv, fp, (int)ctx->cfg.conv, ctx->sm_count, scene_fits_constant(ctx->sv),
                                            ctx->stream, &ctx->launches);

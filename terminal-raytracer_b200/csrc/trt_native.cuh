@@ -234,7 +234,19 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
     constexpr unsigned kRes = kSlots > 1u ? 7u * kSlots : 3u, kB0 = kRes + 1u;
     constexpr unsigned kRec = (kB0 + 1u) | 1u;
     __shared__ float s_lane[TRT_NV_THREADS * kRec];
-    __shared__ float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
+    __shared__ __align__(128) float4 s_tile[SRC::kTileSlots];   // staged geometry of the CTA-cooperative scan (SrcTiled)
+    __shared__ __align__(8) unsigned long long s_mbar[2];       // SrcTiled + TRT_V_TMA_TILES: one mbarrier per tile buffer
+    unsigned tile_phase = 0;
+#ifndef __CUDACC_RTC__
+    if (SRC::kTiled && TRT_V_TMA_TILES) {
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(&s_mbar[0])) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned)__cvta_generic_to_shared(&s_mbar[1])) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+    }
+#endif
     // SrcTiled: second FIFO, of ready shadow rays (origin, direction, contribution, t_max in DQ_RNG, owner in DQ_META)
     __shared__ float s_rays[SRC::kTiled ? TRT_NV_THREADS / 32 : 1][DQ_FIELDS][SRC::kTiled ? TRT_NV_RING : 1];
     const unsigned tid = threadIdx.x, lane = tid & 31u;
@@ -552,9 +564,9 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         if (fp.max_depth != 0u) {
             if (small) t_hit = tr.template scan_small_native<SHAPE>(qo, qd, qt, best);
 #ifndef __CUDACC_RTC__
-            else if (SRC::kTiled) t_hit = tr.scan_native_tiled(qo, qd, mode == NM_ACTIVE || spass ? qt : -1.0f, best, s_tile, spass);
+            else if (SRC::kTiled) t_hit = tr.scan_native_tiled(qo, qd, mode == NM_ACTIVE || spass ? qt : -1.0f, best, s_tile, spass, s_mbar, tile_phase);
 #endif
-            else t_hit = kStrict ? tr.scan_lean(qo, qd, qt, best) : tr.scan_native(qo, qd, qt, best);
+            else t_hit = kStrict ? tr.template scan_lean<typename SHAPE::Runs>(qo, qd, qt, best) : tr.scan_native(qo, qd, qt, best);
         }
 
         if (spass) {                                              // shader.wgsl:402-431 for the queued samples

@@ -95,17 +95,35 @@ struct SrcConst {
     __device__ __forceinline__ float4 le(int k) const { return c_scene.le[k]; }
 };
 
+// Compile-time run list of the strict production scan (scan_lean): (device run type, begin, end) per run, as
+// trt_upload_scene builds them (trt_api.cu: type runs, axis-aligned planes 3..5, slab pairs 6..8).  With a fixed list
+// the run loop, the type dispatch and the inner loops unroll and every operand has a fixed constant-bank address.
+struct RunsAny {
+    static constexpr bool kFixed = false;
+    static constexpr int kCount = 0;
+    static __host__ __device__ __forceinline__ constexpr int4 run(int) { return int4{0, 0, 0, 0}; }
+};
+// the default Cornell box: 3 spheres, slab pairs y (floor / ceiling), x (right / left), z (front / back), 2 triangles
+struct RunsCornell {
+    static constexpr bool kFixed = true;
+    static constexpr int kCount = 5;
+    static __host__ __device__ __forceinline__ constexpr int4 run(int r) {
+        return r == 0 ? int4{0, 0, 3, 0} : r == 1 ? int4{7, 3, 5, 0} : r == 2 ? int4{6, 5, 7, 0} : r == 3 ? int4{8, 7, 9, 0} : int4{2, 9, 11, 0};
+    }
+};
 // Compile-time description of a canonical small scene for scan_small_native: primitive counts, the kind of every
 // plane (2 bits each, first plane in the low bits; kinds as in SmallScene::pl_p.w) and, when NL >= 0, the number of
 // lights and which of them are spheres (bit k of LSPH; the others are triangles).
 struct ShapeAny {
+    typedef RunsAny Runs;
     static constexpr bool kFixed = false, kFixedLights = false;
     static constexpr int NS = 0, NP = 0, NT = 0, NL = -1;
     static __host__ __device__ __forceinline__ constexpr int kind(int) { return 3; }
     static __host__ __device__ __forceinline__ constexpr bool light_is_sphere(int, int type) { return type == 0; }
     static __host__ __device__ __forceinline__ constexpr unsigned tri_zero(int) { return 0u; }
 };
-template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSPH_ = 0u, unsigned TZ_ = 0u> struct ShapeFixed {
+template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSPH_ = 0u, unsigned TZ_ = 0u, class RUNS_ = RunsAny> struct ShapeFixed {
+    typedef RUNS_ Runs;
     static constexpr bool kFixed = true, kFixedLights = NL_ >= 0;
     static constexpr int NS = NS_, NP = NP_, NT = NT_, NL = NL_;
     static constexpr unsigned KINDS = KINDS_, LSPH = LSPH_;
@@ -120,6 +138,7 @@ template <int NS_, int NP_, int NT_, unsigned KINDS_, int NL_ = -1, unsigned LSP
 // the reference's embedded default scene (lib.rs:107, src/scenes/Cornell_Box.json): 3 spheres, floor / ceiling
 // (y), right / left (x), front / back (z) walls, 2 triangles, both of them lights
 typedef ShapeFixed<3, 6, 2, 0xA05u, 2, 0u, 0x4DEu> ShapeCornell;      // light quad: edges along x and z
+typedef ShapeFixed<3, 6, 2, 0xA05u, 2, 0u, 0x4DEu, RunsCornell> ShapeCornellStrict;   // + the strict scan's run list
 
 // Large scenes in the production kernel: the CTA scans together.  Each warp scanning 20 k primitives on its
 // own streams ~1 MB through a 256 KB L1 per scan (C4 measured: 0.65 % of FP32 peak, L2 -> L1 bound); here the
@@ -186,6 +205,12 @@ __device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool
 #endif
 // TRT_V_NO_RENORM: cosine_hemisphere_unit returns u*x + v*y + w*z without the final normalize (:334): (u, v, w) is
 // orthonormal and x^2 + y^2 + z^2 = 1 up to rounding, so the length is 1 +- a few ulp already.  -0.6 % (38.65 -> 38.41 ms).
+// TRT_V_TMA_TILES: the geometry tiles of the CTA-cooperative scan (SrcTiled) are staged by the TMA unit -- one thread
+// issues three cp.async.bulk copies per tile (the SoA arrays ga / gb / gc are contiguous per tile) that complete on an
+// mbarrier -- instead of three cp.async per thread.  0 = the per-thread cp.async staging of round 1 (A/B).
+#ifndef TRT_V_TMA_TILES
+#define TRT_V_TMA_TILES 1
+#endif
 #ifndef TRT_V_NO_RENORM
 #define TRT_V_NO_RENORM 1
 #endif
@@ -336,20 +361,11 @@ struct Tracer {
         return scan_closest(ro, rd, 0.001f, t_max, best, -1);
     }
 
-    __device__ __forceinline__ float scan_lean(float3 ro, float3 rd, float t_max, int &best) {
-        const float t_min = 0.001f;
-        // non-finite rays (never produced by a sane scene) take the as-written code: 0 * inf is NaN there
-        // (origins beyond 1e30 too: there p - o could overflow; x * 1e8 overflows to inf first)
-        float fin = __fmaf_rn(ro.x * 1e8f, 0.0f, 0.0f);
-        fin = __fmaf_rn(ro.y * 1e8f, 0.0f, fin); fin = __fmaf_rn(ro.z * 1e8f, 0.0f, fin);
-        fin = __fmaf_rn(rd.x, 0.0f, fin); fin = __fmaf_rn(rd.y, 0.0f, fin); fin = __fmaf_rn(rd.z, 0.0f, fin);
-        if (!(fin == 0.0f)) return scan_as_written(ro, rd, t_max, best);
-        float closest = t_max;
-        best = -1;
-        for (int r = 0; r < sc.n_runs; r++) {
-            const int4 run = src.run(r);
+    // the tests of one run of scan_lean; `fallback`: an input the shortcuts do not cover (the caller rescans as written)
+    template <int UN>
+    __device__ __forceinline__ void lean_run(const int4 run, float3 ro, float3 rd, float t_min, float &closest, int &best, bool &fallback) {
             if (run.x == 0) {                                   // spheres: as written, accept == (t > 0)
-#pragma unroll SRC::kUnroll
+#pragma unroll UN
                 for (int i = run.y; i < run.z; i++) {
                     uint32_t cost;
                     const float t = test_sphere(ro, rd, src.ga(i), src.gb(i).x, t_min, closest, cost);
@@ -364,14 +380,14 @@ struct Tracer {
                 const float o_a = run.x == 6 ? ro.x : run.x == 7 ? ro.y : ro.z;
                 const float d_a = run.x == 6 ? rd.x : run.x == 7 ? rd.y : rd.z;
                 const bool live = fabsf(d_a) >= 0.0001f;        //  abs(denom) < 0.0001 -> miss (:180)
-#pragma unroll SRC::kUnroll
+#pragma unroll UN
                 for (int i = run.y; i < run.z; i += 2) {
                     const float4 pr = src.gc(i);                // (p_lo, p_hi, 1 if the first plane is p_hi, 2^20 * gap)
                     const bool take_hi = d_a > 0.0f ? !(o_a < pr.x) : (o_a > pr.y);
                     const float num = (take_hi ? pr.y : pr.x) - o_a;
                     const float t = num / d_a;
                     if (live) {
-                        if ((t > 0.0f && t < t_min) || !(fabsf(num) < pr.w)) return scan_as_written(ro, rd, t_max, best);
+                        if ((t > 0.0f && t < t_min) || !(fabsf(num) < pr.w)) { fallback = true; return; }
                         if (t >= t_min && t < closest) { closest = t; best = i + ((take_hi ? 1 : 0) ^ __float2int_rz(pr.z)); }
                     }
                 }
@@ -379,13 +395,13 @@ struct Tracer {
                 const float o_a = run.x == 3 ? ro.x : run.x == 4 ? ro.y : ro.z;
                 const float d_a = run.x == 3 ? rd.x : run.x == 4 ? rd.y : rd.z;
                 const bool live = fabsf(d_a) >= 0.0001f;
-#pragma unroll SRC::kUnroll
+#pragma unroll UN
                 for (int i = run.y; i < run.z; i++) {
                     const float t = (src.ga_axis(i, run.x - 3) - o_a) / d_a;
                     if (live && t >= t_min && t < closest) { closest = t; best = i; }
                 }
             } else if (run.x == 1) {                            // general planes: as written, fused accept
-#pragma unroll SRC::kUnroll
+#pragma unroll UN
                 for (int i = run.y; i < run.z; i++) {
                     const float4 n = src.gb(i);
                     const float denom = V::dot(xyz(n), rd);
@@ -393,7 +409,7 @@ struct Tracer {
                     if (fabsf(denom) >= 0.0001f && t >= t_min && t < closest) { closest = t; best = i; }
                 }
             } else if (run.x == 2) {                            // triangles
-#pragma unroll SRC::kUnroll
+#pragma unroll UN
                 for (int i = run.y; i < run.z; i++) {
                     const float3 e1 = xyz(src.gb(i)), e2 = xyz(src.gc(i));
                     const float3 h = V::cross(rd, e2);
@@ -415,7 +431,27 @@ struct Tracer {
                     if (t > t_min && t < closest) { closest = t; best = i; }
                 }
             }
+    }
+
+    template <class RUNS = RunsAny>
+    __device__ __forceinline__ float scan_lean(float3 ro, float3 rd, float t_max, int &best) {
+        const float t_min = 0.001f;
+        // non-finite rays (never produced by a sane scene) take the as-written code: 0 * inf is NaN there
+        // (origins beyond 1e30 too: there p - o could overflow; x * 1e8 overflows to inf first)
+        float fin = __fmaf_rn(ro.x * 1e8f, 0.0f, 0.0f);
+        fin = __fmaf_rn(ro.y * 1e8f, 0.0f, fin); fin = __fmaf_rn(ro.z * 1e8f, 0.0f, fin);
+        fin = __fmaf_rn(rd.x, 0.0f, fin); fin = __fmaf_rn(rd.y, 0.0f, fin); fin = __fmaf_rn(rd.z, 0.0f, fin);
+        if (!(fin == 0.0f)) return scan_as_written(ro, rd, t_max, best);
+        float closest = t_max;
+        best = -1;
+        bool fallback = false;
+        if (RUNS::kFixed) {
+#pragma unroll
+            for (int r = 0; r < RUNS::kCount; r++) lean_run<16>(RUNS::run(r), ro, rd, t_min, closest, best, fallback);
+        } else {
+            for (int r = 0; r < sc.n_runs && !fallback; r++) lean_run<SRC::kUnroll>(src.run(r), ro, rd, t_min, closest, best, fallback);
         }
+        if (fallback) return scan_as_written(ro, rd, t_max, best);
         return best >= 0 ? closest : -1.0f;
     }
 
@@ -505,13 +541,46 @@ struct Tracer {
     // times.  `tile` = 2 x 3 x TRT_TILE float4 of shared memory.  any_hit: the caller only reads t < 0
     // (shader.wgsl:400-402), so a warp whose lanes have all found an occluder (or have nothing to look for)
     // stops testing; it keeps taking part in the staging and the barriers.
-    __device__ __forceinline__ float scan_native_tiled(float3 ro, float3 rd, float t_max, int &best, float4 *tile, bool any_hit) {
+    // `mbar`: two mbarriers in shared memory (initialised once by the kernel, count 1), `phase`: the parity each of them
+    // completes next (bit b for buffer b), carried by the caller across scans (TRT_V_TMA_TILES)
+    __device__ __forceinline__ float scan_native_tiled(float3 ro, float3 rd, float t_max, int &best, float4 *tile, bool any_hit,
+                                                       unsigned long long *mbar, unsigned &phase) {
         const float t_min = 0.001f;
         float closest = t_max;
         best = -1;
         const float3 inv = f3(rcp_native(rd.x), rcp_native(rd.y), rcp_native(rd.z));
         const int tid = (int)threadIdx.x;
         const int n_tiles = sc.n_tiles;
+#if TRT_V_TMA_TILES
+        auto stage = [&](int k) {
+            if (tid != 0) return;
+            const int4 td = __ldg(&sc.tiles[k]);
+            float4 *buf = tile + (k & 1) * 3 * TRT_TILE;
+            const unsigned bytes = (unsigned)td.z * 16u;
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&mbar[k & 1]);
+            // the buffer was read with ordinary loads up to the barrier the caller has just passed: order them before
+            // the asynchronous proxy's writes
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(3u * bytes) : "memory");
+            const float4 *src[3] = {sc.ga + td.y, sc.gb + td.y, sc.gc + td.y};
+#pragma unroll
+            for (int a = 0; a < 3; a++)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                 (unsigned)__cvta_generic_to_shared(buf + a * TRT_TILE)),
+                             "l"(src[a]), "r"(bytes), "r"(bar)
+                             : "memory");
+        };
+        auto wait_tile = [&](int k) {
+            const unsigned bar = (unsigned)__cvta_generic_to_shared(&mbar[k & 1]);
+            const unsigned parity = (phase >> (k & 1)) & 1u;
+            unsigned done = 0;
+            while (!done)
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+            phase ^= 1u << (k & 1);
+        };
+#else
+        (void)mbar; (void)phase;
         auto stage = [&](int k) {
             const int4 td = __ldg(&sc.tiles[k]);
             float4 *buf = tile + (k & 1) * 3 * TRT_TILE;
@@ -522,10 +591,12 @@ struct Tracer {
             }
             __pipeline_commit();
         };
+        auto wait_tile = [&](int) { __pipeline_wait_prior(0); };
+#endif
         if (n_tiles > 0) stage(0);
         bool warp_done = false;
         for (int k = 0; k < n_tiles; k++) {
-            __pipeline_wait_prior(0);
+            wait_tile(k);
             __syncthreads();                                  // tile k has landed; buffer (k + 1) & 1 is free again
             if (k + 1 < n_tiles) stage(k + 1);
             if (!warp_done) {
