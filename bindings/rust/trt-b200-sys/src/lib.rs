@@ -24,6 +24,8 @@ pub const TRT_CONV_NATIVE: u32 = 2;
 pub const TRT_MODE_ASCII: c_int = 0;
 pub const TRT_MODE_TRUECOLOR: c_int = 1;
 pub const TRT_MODE_NONE: c_int = 2;
+pub const TRT_ACCEL_NONE: u32 = 0;
+pub const TRT_ACCEL_GRID: u32 = 1;
 pub const TRT_KEY_UP: c_int = 1001;
 pub const TRT_KEY_DOWN: c_int = 1002;
 pub const TRT_KEY_LEFT: c_int = 1003;
@@ -69,7 +71,8 @@ pub struct trt_config {
     pub abi_version: u32, pub device: i32, pub max_width: u32, pub max_height: u32,
     pub conv: u32, pub count_work: u32,
     pub shard_index: u32, pub shard_count: u32, pub stripe_rows: u32,
-    pub reserved: [u32; 7],
+    pub accel: u32,
+    pub reserved: [u32; 6],
 }
 
 #[repr(C)] #[derive(Clone, Copy, Default, Debug)]
@@ -99,7 +102,7 @@ pub struct trt_scene_info {
 pub struct trt_run_options {
     pub width: u32, pub height: u32, pub frames: u32, pub seed: u32, pub has_seed: u32,
     pub keys: *const c_char, pub out_path: *const c_char,
-    pub device: i32, pub conv: u32, pub quiet: u32, pub batch_frames: u32, pub gpus: u32, pub pipeline: u32,
+    pub device: i32, pub conv: u32, pub quiet: u32, pub batch_frames: u32, pub gpus: u32, pub accel: u32, pub pipeline: u32,
 }
 
 extern "C" {
@@ -264,7 +267,7 @@ impl Drop for MultiTracer { fn drop(&mut self) { unsafe { trt_free_host(self.out
 pub fn run(full_color: bool, verbose: bool, scene_path: Option<&str>) -> Result<(), Error> {
     let path = scene_path.map(|p| std::ffi::CString::new(p).expect("path contains NUL"));
     let opts = trt_run_options { width: 0, height: 0, frames: 0, seed: 0, has_seed: 0, keys: std::ptr::null(), out_path: std::ptr::null(),
-                                 device: 0, conv: TRT_CONV_NATIVE, quiet: 0, batch_frames: 0, gpus: 0, pipeline: 0 };
+                                 device: 0, conv: TRT_CONV_NATIVE, quiet: 0, batch_frames: 0, gpus: 0, accel: 0, pipeline: 0 };
     let rc = unsafe { trt_run(full_color as c_int, verbose as c_int, path.as_ref().map_or(std::ptr::null(), |p| p.as_ptr()), &opts) };
     if rc == TRT_OK { Ok(()) } else { Err(Error { code: rc, message: "trt_run failed (see stderr)".into() }) }
 }

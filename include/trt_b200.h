@@ -92,6 +92,9 @@ typedef struct trt_ctx trt_ctx;
 #define TRT_MODE_TRUECOLOR  1
 #define TRT_MODE_NONE       2     /* trace + accumulate only, no byte stream */
 
+#define TRT_ACCEL_NONE      0
+#define TRT_ACCEL_GRID      1
+
 typedef struct trt_config {
     uint32_t abi_version;         /* TRT_ABI_VERSION */
     int32_t  device;              /* CUDA device ordinal (one context = one GPU) */
@@ -103,7 +106,11 @@ typedef struct trt_config {
      * and RNG seeds always use the global (x, y, width): the union of the shards' rows is
      * bit-identical to a single-context frame.  shard_count 0 or 1 = whole frame. */
     uint32_t shard_index, shard_count, stripe_rows;
-    uint32_t reserved[7];
+    /* TRT_ACCEL_NONE: the reference's linear scan (the parity contract).  TRT_ACCEL_GRID (opt-in, conv 2 only, outside the
+     * parity contract, reported separately): hit_scene through the uniform grid the reference builds and never uses
+     * (lib.rs:181-244): same (t, index) per ray, O(cells) instead of O(primitives) tests. */
+    uint32_t accel;
+    uint32_t reserved[6];
 } trt_config;
 
 /* work counters of the instrumented build (same fields as the oracle's) */
@@ -293,6 +300,7 @@ typedef struct trt_run_options {
                                    * (trt_render_frames) and show the last one; 0 / 1: one frame per round trip as
                                    * the reference does */
     uint32_t gpus;                /* > 1: every frame row-sharded over devices device .. device + gpus - 1 (trt_multi) */
+    uint32_t accel;               /* TRT_ACCEL_*: opt-in acceleration structure (conv 2) */
     uint32_t pipeline;            /* 1: frame f is copied back and written while frame f + 1 is traced
                                    * (trt_frame_submit / trt_frame_collect); same frames, same bytes, same order */
 } trt_run_options;

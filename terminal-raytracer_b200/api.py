@@ -19,6 +19,7 @@ LIB_PATH = os.environ.get("TRT_B200_LIB") or os.path.join(HERE, "libtrt_b200.so"
 TRT_ABI_VERSION = 1
 CONV_AS_WRITTEN, CONV_FUSED, CONV_NATIVE = 0, 1, 2
 MODE_ASCII, MODE_TRUECOLOR, MODE_NONE = 0, 1, 2
+ACCEL_NONE, ACCEL_GRID = 0, 1
 KEY_UP, KEY_DOWN, KEY_LEFT, KEY_RIGHT = 1001, 1002, 1003, 1004
 KEYS = {"w": ord("w"), "a": ord("a"), "s": ord("s"), "d": ord("d"),
         "Up": KEY_UP, "Down": KEY_DOWN, "Left": KEY_LEFT, "Right": KEY_RIGHT}
@@ -57,7 +58,7 @@ class Config(C.Structure):
     _fields_ = [("abi_version", C.c_uint32), ("device", C.c_int32), ("max_width", C.c_uint32), ("max_height", C.c_uint32),
                 ("conv", C.c_uint32), ("count_work", C.c_uint32),
                 ("shard_index", C.c_uint32), ("shard_count", C.c_uint32), ("stripe_rows", C.c_uint32),
-                ("reserved", C.c_uint32 * 7)]
+                ("accel", C.c_uint32), ("reserved", C.c_uint32 * 6)]
 
 
 COUNTER_FIELDS = ["pixels", "samples_base", "samples_extra", "closest_scans", "hits", "misses", "shadow_scans",
@@ -92,7 +93,7 @@ class RunOptions(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("frames", C.c_uint32), ("seed", C.c_uint32),
                 ("has_seed", C.c_uint32), ("keys", C.c_char_p), ("out_path", C.c_char_p), ("device", C.c_int32),
                 ("conv", C.c_uint32), ("quiet", C.c_uint32), ("batch_frames", C.c_uint32), ("gpus", C.c_uint32),
-                ("pipeline", C.c_uint32)]
+                ("accel", C.c_uint32), ("pipeline", C.c_uint32)]
 
 
 assert C.sizeof(Vec3) == 16 and C.sizeof(Primitive) == 180 and C.sizeof(Uniforms) == 160
@@ -269,10 +270,10 @@ class Renderer:
     byte stream back (the wgpu section of the reference's frame loop, lib.rs:442-477 + 503-532)."""
 
     def __init__(self, max_width, max_height, device=0, conv=CONV_AS_WRITTEN, count_work=False,
-                 shard_index=0, shard_count=1, stripe_rows=1):
+                 shard_index=0, shard_count=1, stripe_rows=1, accel=0):
         cfg = Config(abi_version=TRT_ABI_VERSION, device=device, max_width=max_width, max_height=max_height,
                      conv=conv, count_work=1 if count_work else 0, shard_index=shard_index,
-                     shard_count=shard_count, stripe_rows=stripe_rows)
+                     shard_count=shard_count, stripe_rows=stripe_rows, accel=accel)
         self.h = _P()
         self.max_pixels = max_width * max_height
         rc = lib().trt_create(C.byref(cfg), C.byref(self.h))

@@ -90,6 +90,9 @@ struct trt_ctx {
     SceneView sv{};
     LightView lv{};
     SmallScene small{};                // canonical small-scene mirror for the conv 2 scan (host copy)
+    // opt-in uniform grid (trt_config.accel)
+    uint32_t *d_grid_off = nullptr, *d_grid_idx = nullptr;
+    int *d_grid_planes = nullptr;
     bool have_scene = false;
     bool cornell_runs = false;         // the scene has the default Cornell layout incl. its run list (RunsCornell)
     uint64_t scene_serial = 0;
@@ -194,7 +197,7 @@ extern "C" void trt_destroy(trt_ctx *ctx) {
     void *ptrs[] = {ctx->d_aos, ctx->d_geom, ctx->d_type, ctx->d_runs, ctx->d_tiles, ctx->d_lights, ctx->d_light_prim, ctx->d_lgeom,
                     ctx->d_pixels, ctx->d_accum, ctx->d_variance, ctx->d_counters, ctx->d_work, ctx->d_stats, ctx->d_row_map, ctx->d_order,
                     ctx->d_cost, ctx->d_row_src, ctx->d_packed, ctx->d_block_len, ctx->d_block_off, ctx->d_stream, ctx->d_batch_cur, ctx->d_batch, ctx->d_batch_stream,
-                    ctx->d_row_len, ctx->d_row_src_g, ctx->d_stream2, ctx->d_tile_state, ctx->d_row_start};
+                    ctx->d_row_len, ctx->d_row_src_g, ctx->d_stream2, ctx->d_tile_state, ctx->d_row_start, ctx->d_grid_off, ctx->d_grid_idx, ctx->d_grid_planes};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (ctx->h_len) cudaFreeHost(ctx->h_len);
     if (ctx->h_row_len) cudaFreeHost(ctx->h_row_len);
@@ -214,6 +217,10 @@ extern "C" int trt_create(const trt_config *cfg, trt_ctx **out) {
     if (cfg->abi_version != TRT_ABI_VERSION) return fail(nullptr, TRT_ERR_INVALID, "trt_create: ABI version mismatch");
     if (cfg->max_width == 0 || cfg->max_height == 0) return fail(nullptr, TRT_ERR_INVALID, "trt_create: zero frame size");
     if (cfg->conv > 2u) return fail(nullptr, TRT_ERR_INVALID, "trt_create: unknown arithmetic convention");
+    if (cfg->accel > TRT_ACCEL_GRID) return fail(nullptr, TRT_ERR_INVALID, "trt_create: unknown acceleration structure");
+    if (cfg->accel != TRT_ACCEL_NONE && (cfg->conv != TRT_CONV_NATIVE || cfg->count_work))
+        return fail(nullptr, TRT_ERR_INVALID, "trt_create: the acceleration structure is an opt-in of the native convention (the strict "
+                                              "builds and the work counters follow the reference's linear scan)");
     if (cfg->shard_count > 1u && cfg->shard_index >= cfg->shard_count)
         return fail(nullptr, TRT_ERR_INVALID, "trt_create: shard_index >= shard_count");
     int n_dev = 0;
@@ -442,6 +449,90 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     ctx->sv.type = ctx->d_type; ctx->sv.runs = ctx->d_runs; ctx->sv.lights = ctx->d_lights;
     ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;
     ctx->sv.tiles = ctx->d_tiles; ctx->sv.n_tiles = (int)tiles.size();
+    // ---- opt-in uniform grid: the reference's build_uniform_grid (lib.rs:181-244) over spheres and triangles -------
+    ctx->sv.grid_off = ctx->sv.grid_idx = nullptr; ctx->sv.grid_planes = nullptr; ctx->sv.n_grid_planes = 0;
+    if (ctx->cfg.accel == TRT_ACCEL_GRID && count) {
+        auto aabb = [&](const trt_primitive &p, float mn[3], float mx[3]) -> bool {      // lib.rs:158-179
+            if (p.primitive_type == 0u) {
+                const float c[3] = {p.sphere_center.x, p.sphere_center.y, p.sphere_center.z}, r = fabsf(p.sphere_radius);
+                for (int a = 0; a < 3; a++) { mn[a] = c[a] - r; mx[a] = c[a] + r; }
+                return true;
+            }
+            if (p.primitive_type == 2u) {
+                const float v[3][3] = {{p.triangle_v0.x, p.triangle_v0.y, p.triangle_v0.z}, {p.triangle_v1.x, p.triangle_v1.y, p.triangle_v1.z},
+                                       {p.triangle_v2.x, p.triangle_v2.y, p.triangle_v2.z}};
+                for (int a = 0; a < 3; a++) { mn[a] = fminf(v[0][a], fminf(v[1][a], v[2][a])); mx[a] = fmaxf(v[0][a], fmaxf(v[1][a], v[2][a])); }
+                return true;
+            }
+            return false;
+        };
+        float bmin[3] = {INFINITY, INFINITY, INFINITY}, bmax[3] = {-INFINITY, -INFINITY, -INFINITY};
+        std::vector<int> plane_list;
+        uint32_t bounded = 0;
+        for (uint32_t i = 0; i < count; i++) {
+            float mn[3], mx[3];
+            if (aabb(prims[i], mn, mx)) { bounded++; for (int a = 0; a < 3; a++) { bmin[a] = fminf(bmin[a], mn[a]); bmax[a] = fmaxf(bmax[a], mx[a]); } }
+            else if (prims[i].primitive_type == 1u) plane_list.push_back((int)i);
+        }
+        if (bounded) {
+            for (int a = 0; a < 3; a++) { bmin[a] -= 1e-3f; bmax[a] += 1e-3f; }                         // lib.rs:191-193
+            const float ext[3] = {bmax[0] - bmin[0], bmax[1] - bmin[1], bmax[2] - bmin[2]};
+            const float emax = fmaxf(ext[0], fmaxf(ext[1], ext[2]));
+            const float sres = cbrtf((float)bounded) * 1.5f;                                            // lib.rs:196-198
+            int dims[3];
+            for (int a = 0; a < 3; a++) { dims[a] = (int)lroundf(fmaxf(sres * (ext[a] / emax), 1.0f)); if (dims[a] < 1) dims[a] = 1; if (dims[a] > 256) dims[a] = 256; }
+            const float cell[3] = {ext[0] / dims[0], ext[1] / dims[1], ext[2] / dims[2]};
+            const size_t n_cells = (size_t)dims[0] * dims[1] * dims[2];
+            std::vector<uint32_t> off(n_cells + 1, 0);
+            auto range = [&](const float mn[3], const float mx[3], int lo[3], int hi[3]) {
+                for (int a = 0; a < 3; a++) {
+                    lo[a] = (int)fminf(fmaxf(floorf((mn[a] - bmin[a]) / cell[a]), 0.0f), (float)(dims[a] - 1));
+                    hi[a] = (int)fminf(fmaxf(floorf((mx[a] - bmin[a]) / cell[a]), 0.0f), (float)(dims[a] - 1));
+                }
+            };
+            for (int pass = 0; pass < 2; pass++) {                       // count, then fill (primitive order = scan order)
+                std::vector<uint32_t> cur;
+                std::vector<uint32_t> idx;
+                if (pass == 1) {
+                    uint32_t run = 0;
+                    for (size_t c = 0; c < n_cells; c++) { const uint32_t n = off[c]; off[c] = run; run += n; }
+                    off[n_cells] = run;
+                    cur.assign(off.begin(), off.end() - 1);
+                    idx.resize(run);
+                }
+                for (uint32_t i = 0; i < count; i++) {
+                    float mn[3], mx[3];
+                    if (!aabb(prims[i], mn, mx)) continue;
+                    int lo[3], hi[3];
+                    range(mn, mx, lo, hi);
+                    for (int z = lo[2]; z <= hi[2]; z++)
+                        for (int y = lo[1]; y <= hi[1]; y++)
+                            for (int x = lo[0]; x <= hi[0]; x++) {
+                                const size_t c = (size_t)x + (size_t)dims[0] * ((size_t)y + (size_t)dims[1] * z);
+                                if (pass == 0) off[c]++; else idx[cur[c]++] = i;
+                            }
+                }
+                if (pass == 1) {
+                    if (ctx->d_grid_off) cudaFree(ctx->d_grid_off);
+                    if (ctx->d_grid_idx) cudaFree(ctx->d_grid_idx);
+                    if (ctx->d_grid_planes) cudaFree(ctx->d_grid_planes);
+                    ctx->d_grid_off = ctx->d_grid_idx = nullptr; ctx->d_grid_planes = nullptr;
+                    CK(cudaMalloc(&ctx->d_grid_off, off.size() * sizeof(uint32_t)));
+                    CK(cudaMalloc(&ctx->d_grid_idx, (idx.size() + 1) * sizeof(uint32_t)));
+                    CK(cudaMalloc(&ctx->d_grid_planes, (plane_list.size() + 1) * sizeof(int)));
+                    CK(cudaMemcpy(ctx->d_grid_off, off.data(), off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+                    if (!idx.empty()) CK(cudaMemcpy(ctx->d_grid_idx, idx.data(), idx.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+                    if (!plane_list.empty()) CK(cudaMemcpy(ctx->d_grid_planes, plane_list.data(), plane_list.size() * sizeof(int), cudaMemcpyHostToDevice));
+                }
+            }
+            ctx->sv.grid_off = ctx->d_grid_off; ctx->sv.grid_idx = ctx->d_grid_idx;
+            ctx->sv.grid_planes = ctx->d_grid_planes; ctx->sv.n_grid_planes = (int)plane_list.size();
+            ctx->sv.gx = dims[0]; ctx->sv.gy = dims[1]; ctx->sv.gz = dims[2];
+            ctx->sv.grid_min = make_float3(bmin[0], bmin[1], bmin[2]);
+            ctx->sv.grid_cell = make_float3(cell[0], cell[1], cell[2]);
+            ctx->sv.grid_inv_cell = make_float3(1.0f / cell[0], 1.0f / cell[1], 1.0f / cell[2]);
+        }
+    }
     {   // default Cornell layout (ShapeCornell) with exactly the run list RunsCornell: the strict specialised kernel
         bool c = ctx->small.ok && ctx->small.n_sph == ShapeCornell::NS && ctx->small.n_pl == ShapeCornell::NP &&
                  ctx->small.n_tri == ShapeCornell::NT && n_lights == (uint32_t)ShapeCornell::NL && ctx->small.n_light_spheres == 0 &&

@@ -40,6 +40,14 @@ struct SceneView {
     // the CTA-cooperative scan of large scenes stages one tile at a time in shared memory (trt_trace.cuh)
     const int4 *tiles;
     int n_tiles;
+    // opt-in acceleration structure (trt_config.accel = TRT_ACCEL_GRID; OUTSIDE the parity contract's linear scan, though
+    // it returns the same (t, index)): the reference's abandoned uniform grid (lib.rs:181-244) over spheres and
+    // triangles -- CSR cell lists in scan order -- plus the list of planes (unbounded: always tested).  NULL = none.
+    const uint32_t *grid_off, *grid_idx;
+    const int *grid_planes;
+    int n_grid_planes;
+    int gx, gy, gz;
+    float3 grid_min, grid_cell, grid_inv_cell;
 };
 #define TRT_TILE 128
 

@@ -35,6 +35,7 @@ int main(int argc, char **argv) {
         else if (a == "--batch" && next) o.batch_frames = (uint32_t)strtoul(next, nullptr, 10);
         else if (a == "--quiet") o.quiet = 1;
         else if (a == "--gpus" && next) o.gpus = (uint32_t)strtoul(next, nullptr, 10);     // rows of every frame over N devices
+        else if (a == "--accel" && next) o.accel = !strcmp(next, "grid") ? TRT_ACCEL_GRID : TRT_ACCEL_NONE;   // opt-in, outside the parity contract
         else if (a == "--pipeline") o.pipeline = 1;                                        // overlap copy + stdout with the next frame's trace
     }
     if (threads <= 0) {                                                    // main.rs:18-19

@@ -84,7 +84,15 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         }
     }
     const char *name = "";
-    if (jk) {
+    if (sv.grid_off) {
+        // opt-in acceleration structure: persistent lanes, every lane walks the grid for its own ray
+        const uint32_t wwant = (n_work + TRT_WV_THREADS - 1u) / TRT_WV_THREADS;
+        const uint32_t wcap = (uint32_t)sm_count * TRT_WV_CTAS_PER_SM;
+        const uint32_t wblocks = wwant < wcap ? wwant : wcap;
+        if (fp.batch) trace_wave_kernel<2, SrcGrid, true><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_wave_kernel<2, SrcGrid, false><<<wblocks, TRT_WV_THREADS, 0, stream>>>(sv, lv, fp);
+        name = "trace_wave_kernel<2, SrcGrid> (uniform grid, opt-in)";
+    } else if (jk) {
         void *args[] = {(void *)&sv, (void *)&lv, (void *)&fp};
         e = cudaLaunchKernel((const void *)jk->kernel, dim3(blocks), dim3(TRT_NV_THREADS), args, 0, stream);
         if (e != cudaSuccess) return e;

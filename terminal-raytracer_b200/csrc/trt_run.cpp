@@ -102,6 +102,7 @@ extern "C" int trt_run(int full_color, int verbose, const char *scene_path, cons
     cfg.max_width = info.width;
     cfg.max_height = info.height;
     cfg.conv = opts.conv;
+    cfg.accel = opts.conv == TRT_CONV_NATIVE ? opts.accel : TRT_ACCEL_NONE;
     trt_ctx *ctx = nullptr;
     trt_multi *multi = nullptr;                                  // --gpus N: every frame row-sharded over N devices
     if (opts.gpus > 1u) {

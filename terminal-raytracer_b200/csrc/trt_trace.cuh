@@ -56,6 +56,7 @@ struct SmallScene {
 TRT_CONSTANT(SmallScene c_small);
 
 struct SrcGlobal {
+    static constexpr bool kGrid = false;
     static constexpr bool kSmall = false;
     static constexpr bool kTiled = false;     // every warp reads the geometry on its own (L1 / L2)
     static constexpr int kTileSlots = 1;
@@ -76,6 +77,7 @@ struct SrcGlobal {
     __device__ __forceinline__ float4 le(int k) const { return __ldg(&lv.le[k]); }
 };
 struct SrcConst {
+    static constexpr bool kGrid = false;
     static constexpr bool kSmall = true;     // the canonical small-scene mirror may be used (c_small.ok)
     static constexpr bool kTiled = false;
     static constexpr int kTileSlots = 1;
@@ -145,6 +147,11 @@ typedef ShapeFixed<3, 6, 2, 0xA05u, 2, 0u, 0x4DEu, RunsCornell> ShapeCornellStri
 // four warps of a CTA walk the scene in step, tile by tile: TRT_TILE primitives (3 x float4 each) are staged
 // in shared memory with cp.async, double-buffered, and every lane tests its own ray against the tile through
 // conflict-free broadcast reads.  Light data and hit records still come through the read-only path.
+// Large scenes through the opt-in uniform grid (scan_grid): geometry through the read-only path, per-lane traversal.
+struct SrcGrid : SrcGlobal {
+    static constexpr bool kGrid = true;
+    __device__ SrcGrid(const SceneView &s, const LightView &l) : SrcGlobal(s, l) {}
+};
 struct SrcTiled : SrcGlobal {
     static constexpr bool kTiled = true;
     static constexpr int kTileSlots = 2 * 3 * TRT_TILE;      // two buffers of (ga, gb, gc)[TRT_TILE]
@@ -533,6 +540,66 @@ struct Tracer {
         best = -1;
         const float3 inv = f3(rcp_native(rd.x), rcp_native(rd.y), rcp_native(rd.z));
         for (int r = 0; r < sc.n_runs; r++) scan_run<SRC::kUnroll>(src, src.run(r), ro, rd, inv, t_min, closest, best);
+        return best >= 0 ? closest : -1.0f;
+    }
+
+    // ---- opt-in: hit_scene through the uniform grid (lib.rs:181-244 built one and never used it) ----------------
+    // 3-D DDA over the cells the ray crosses; a cell's primitives are tested with the same functions as the linear
+    // scan, a hit counts once its t lies inside the cell being visited (a primitive spans several cells), and the walk
+    // stops when the best hit lies before the next cell.  Candidates are compared as (t, index) pairs, lowest index on
+    // equal t, so the result is the linear scan's `first primitive wins ties` (shader.wgsl:279) -- but this is an
+    // acceleration structure the reference does not execute: outside the parity contract, opt-in, reported separately.
+    __device__ __forceinline__ float scan_grid(float3 ro, float3 rd, float t_max, int &best) {
+        const float t_min = 0.001f;
+        float closest = t_max;
+        best = -1;
+        auto consider = [&](int i, int type) {
+            uint32_t cost;
+            const float t = test_any(type, i, ro, rd, t_min, type == 0 ? closest : closest * 1.0000005f + 1e-30f, cost);
+            if (t > 0.0f && (t < closest || (t == closest && i < best))) { closest = t; best = i; }
+        };
+        for (int k = 0; k < sc.n_grid_planes; k++) consider(__ldg(&sc.grid_planes[k]), 1);
+        if (!(t_max > t_min)) return -1.0f;
+        // clip the ray to the grid's box
+        const float3 inv = f3(rcp_native(rd.x), rcp_native(rd.y), rcp_native(rd.z));
+        const float3 hi = f3(sc.grid_min.x + sc.grid_cell.x * sc.gx, sc.grid_min.y + sc.grid_cell.y * sc.gy, sc.grid_min.z + sc.grid_cell.z * sc.gz);
+        float t0 = t_min, t1 = closest;
+        {
+            const float ax = (sc.grid_min.x - ro.x) * inv.x, bx = (hi.x - ro.x) * inv.x;
+            const float ay = (sc.grid_min.y - ro.y) * inv.y, by = (hi.y - ro.y) * inv.y;
+            const float az = (sc.grid_min.z - ro.z) * inv.z, bz = (hi.z - ro.z) * inv.z;
+            t0 = fmaxf(t0, fmaxf(fminf(ax, bx), fmaxf(fminf(ay, by), fminf(az, bz))));
+            t1 = fminf(t1, fminf(fmaxf(ax, bx), fminf(fmaxf(ay, by), fmaxf(az, bz))));
+        }
+        if (!(t0 <= t1)) return best >= 0 ? closest : -1.0f;
+        const float3 p = f3(ro.x + rd.x * t0, ro.y + rd.y * t0, ro.z + rd.z * t0);
+        int cx = min(max((int)floorf((p.x - sc.grid_min.x) * sc.grid_inv_cell.x), 0), sc.gx - 1);
+        int cy = min(max((int)floorf((p.y - sc.grid_min.y) * sc.grid_inv_cell.y), 0), sc.gy - 1);
+        int cz = min(max((int)floorf((p.z - sc.grid_min.z) * sc.grid_inv_cell.z), 0), sc.gz - 1);
+        const int sx = rd.x > 0.0f ? 1 : -1, sy = rd.y > 0.0f ? 1 : -1, sz = rd.z > 0.0f ? 1 : -1;
+        const float big = 3.0e38f;
+        // t at which the ray leaves the current cell along each axis, and the t per cell step
+        float nx = fabsf(rd.x) > 1e-20f ? (sc.grid_min.x + sc.grid_cell.x * (cx + (sx > 0 ? 1 : 0)) - ro.x) * inv.x : big;
+        float ny = fabsf(rd.y) > 1e-20f ? (sc.grid_min.y + sc.grid_cell.y * (cy + (sy > 0 ? 1 : 0)) - ro.y) * inv.y : big;
+        float nz = fabsf(rd.z) > 1e-20f ? (sc.grid_min.z + sc.grid_cell.z * (cz + (sz > 0 ? 1 : 0)) - ro.z) * inv.z : big;
+        const float dx = fabsf(rd.x) > 1e-20f ? fabsf(sc.grid_cell.x * inv.x) : big;
+        const float dy = fabsf(rd.y) > 1e-20f ? fabsf(sc.grid_cell.y * inv.y) : big;
+        const float dz = fabsf(rd.z) > 1e-20f ? fabsf(sc.grid_cell.z * inv.z) : big;
+        for (;;) {
+            const float t_exit = fminf(nx, fminf(ny, nz));
+            const int cell = cx + sc.gx * (cy + sc.gy * cz);
+            const uint32_t b = __ldg(&sc.grid_off[cell]), e = __ldg(&sc.grid_off[cell + 1]);
+            for (uint32_t k = b; k < e; k++) {
+                const int i = (int)__ldg(&sc.grid_idx[k]);
+                consider(i, (int)__ldg(&sc.type[i]));
+            }
+            // a hit inside the cells visited so far ends the walk (margin: the cell boundary's own rounding)
+            if (best >= 0 && closest <= t_exit * 1.000001f + 1e-6f) break;
+            if (t_exit >= t1) break;
+            if (nx <= ny && nx <= nz) { cx += sx; nx += dx; if (cx < 0 || cx >= sc.gx) break; }
+            else if (ny <= nz) { cy += sy; ny += dy; if (cy < 0 || cy >= sc.gy) break; }
+            else { cz += sz; nz += dz; if (cz < 0 || cz >= sc.gz) break; }
+        }
         return best >= 0 ? closest : -1.0f;
     }
 

@@ -110,7 +110,8 @@ trace_wave_kernel(SceneView sc, LightView lv, FrameParams fp) {
         if (CONV == 2) {
             // every lane scans (finished lanes keep a stale ray and ignore the result): uniform control flow
             if (fp.max_depth != 0u)
-                t_hit = (SRC::kSmall && c_small.ok) ? tr.template scan_small_native<ShapeAny>(ro, rd, t_max, best) : tr.scan_native(ro, rd, t_max, best);
+                t_hit = SRC::kGrid ? tr.scan_grid(ro, rd, t_max, best)
+                        : (SRC::kSmall && c_small.ok) ? tr.template scan_small_native<ShapeAny>(ro, rd, t_max, best) : tr.scan_native(ro, rd, t_max, best);
         } else if (mode != WM_DONE && fp.max_depth != 0u) {
             t_hit = tr.scan_lean(ro, rd, t_max, best);
         }
