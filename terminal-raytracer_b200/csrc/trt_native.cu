@@ -45,7 +45,8 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
     const bool force_generic = force && !strcmp(force, "generic");
     const bool force_untiled = force && !strcmp(force, "untiled");     // large scenes: every warp scans on its own
     const bool constant = scene_fits_constant(sv);
-    static bool carveout_set = false;
+    static bool carveout_done[64] = {};          // the attribute applies per device (one process may drive several GPUs)
+    bool &carveout_set = carveout_done[device >= 0 && device < 64 ? device : 0];
     if (!carveout_set) {
         cudaFuncSetAttribute(trace_native_kernel<2, SrcConst, ShapeCornell>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<2, SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
