@@ -721,7 +721,8 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
 }
 
 #ifndef TRT_NV_STRICT_CTAS
-#define TRT_NV_STRICT_CTAS 6     // strict builds: 80 registers (IEEE division / square-root sequences), 34 KB of shared memory
+#define TRT_NV_STRICT_CTAS 5     // strict builds: 96 registers (IEEE division / square-root sequences; 80 spill), 34 KB of shared
+                                 // memory.  Cornell 1920x1080 x 256 spp, conv 0: 6 CTAs 2164, 5 CTAs 2289, 4 CTAs 2080 Msamples/s
 #endif
 template <int CONV, class SRC, class SHAPE>
 __global__ void __launch_bounds__(TRT_NV_THREADS, CONV != 2 ? TRT_NV_STRICT_CTAS : SRC::kCtasPerSm ? SRC::kCtasPerSm : TRT_NV_CTAS_PER_SM)
