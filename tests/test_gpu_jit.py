@@ -45,7 +45,7 @@ def test_which_kernel_runs(pkg, O):
     _, name, _, _ = _render(pkg, O, cornell, 40, 20, 2)
     assert name in ("trace_native_kernel<SrcConst, ShapeCornell>",) or name.startswith("trt_jit_trace<SrcConst, ShapeFixed<3, 6, 2, 0xa05u, 2, 0x0u>")
     _, name, _, _ = _render(pkg, O, cornell, 40, 20, 0)
-    assert name == "trace_wave_kernel<CONV, SrcConst>"
+    assert name == "trace_native_kernel<CONV, SrcConst, ShapeCornell> (strict)"      # the same machine, strict arithmetic
     big = O.make_c4_scene(n_spheres=200, n_tris=300, width=40, height=20, spp=8, max_depth=2)
     _, name, _, _ = _render(pkg, O, big, 40, 20, 2, depth=2)
     assert name == "trace_native_kernel<SrcTiled, ShapeAny>"
