@@ -514,7 +514,8 @@ def main():
     ap.add_argument("--conv", type=int, default=2, choices=[0, 1, 2],
                     help="arithmetic convention: 2 device-native (default, the production build), 0 strict IEEE as written, 1 fused helpers")
     ap.add_argument("--no-strict", action="store_true", help="skip the strict (conv 0) comparison leg")
-    ap.add_argument("--stripe-rows", type=int, default=4)
+    ap.add_argument("--stripe-rows", type=int, default=1,
+                    help="rows per stripe of the round-robin row deal (1: every 8th row per rank at N = 8; tools/shard_sweep.py)")
     ap.add_argument("--count-stride", type=int, default=24, help="instrumented kernel runs on every n-th row")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")

@@ -235,7 +235,7 @@ int trt_frame_submit(trt_ctx *ctx, const trt_uniforms *u, int mode);
 int trt_frame_collect(trt_ctx *ctx, uint8_t *out, size_t cap, size_t *len);
 
 /* ---- one frame over several GPUs of one process (the reference has one device: lib.rs:248-250) --------
- * One row-sharded context per device (cfg->device / shard_* are filled in; stripe_rows 0 = 4).  render_frame has
+ * One row-sharded context per device (cfg->device / shard_* are filled in; stripe_rows 0 = 1).  render_frame has
  * trt_render_frame's contract: blocks until the assembled stream is in `out` (pinned memory lets the GPUs copy
  * concurrently); the stream is byte-identical to a single-GPU frame. */
 typedef struct trt_multi trt_multi;

@@ -86,7 +86,7 @@ class _DevArray:
 class ShardedRenderer:
     """One rank's part of a row-sharded frame.  Needs torch.distributed initialised (NCCL on GPUs)."""
 
-    def __init__(self, pkg, width, height, rank, world, stripe_rows=4, device=0, conv=0):
+    def __init__(self, pkg, width, height, rank, world, stripe_rows=1, device=0, conv=0):
         import torch
         import torch.distributed as dist
         self.torch, self.dist, self.pkg = torch, dist, pkg
