@@ -720,8 +720,14 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
             // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)
             static const bool use_v1 = [] { const char *k = getenv("TRT_B200_KERNEL"); return k && !strcmp(k, "v1"); }();
-            static const bool use_wave = [] { const char *k = getenv("TRT_B200_STRICT"); return k && !strcmp(k, "wave"); }();
-            const bool deferred = !use_v1 && !use_wave && ctx->sv.n_lights <= TRT_NV_MAX_LIGHTS;
+            // Strict kernels: the deferred-NEE machine where its scan has a compile-time run list (the default Cornell
+            // layout: 2 289 against 1 813 Msamples/s), else the round-1 wave kernel (faster than the deferred machine with
+            // the run-time run loop: 1 813 against 1 664).  TRT_B200_STRICT=wave / deferred / generic force one of them
+            // (deferred: the machine on every scene, the configuration the bit-exactness tests of the machine use).
+            static const char *strict_env = getenv("TRT_B200_STRICT");
+            const bool use_wave = strict_env && !strcmp(strict_env, "wave");
+            const bool force_deferred = strict_env && (!strcmp(strict_env, "deferred") || !strcmp(strict_env, "generic"));
+            const bool deferred = !use_v1 && !use_wave && ctx->sv.n_lights <= TRT_NV_MAX_LIGHTS && (ctx->cornell_runs || force_deferred);
             if (e == cudaSuccess) {
                 if (deferred) {
                     if (!n_batch) fp.cost = ctx->d_cost;

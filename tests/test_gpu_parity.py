@@ -213,3 +213,23 @@ def test_mixed_plane_kinds_and_run_order(pkg, O):
             r.close()
             bad = int((_bits(got) != _bits(ref["pixels"])).any(axis=1).sum())
             assert bad == 0, f"conv {conv}: {bad} pixels differ"
+
+
+def test_deferred_machine_is_bit_exact_on_every_scene(tmp_path):
+    """The production kernel's machine (deferred NEE, parking, ordered late sums) in the strict conventions, forced onto
+    every scene (by default it serves the default Cornell layout, where its scan is specialised; the wave kernel serves the
+    others): the strict frame tests of this file and the golden fixtures, in a process with TRT_B200_STRICT=deferred."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TRT_B200_STRICT="deferred")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-x",
+                        os.path.join(root, "tests", "test_gpu_parity.py"), os.path.join(root, "tests", "test_golden.py"),
+                        os.path.join(root, "tests", "test_gpu_edges.py"), "-k", "not deferred_machine"],
+                       env=env, capture_output=True, text=True, timeout=900, cwd=root)
+    assert r.returncode == 0, r.stdout[-3000:]
+    probe = ("import json,os,sys; sys.path.insert(0, %r); import __graft_entry__ as g; pkg, O = g.load_package(), g.load_oracle(); "
+             "prims = O.flatten_scene(O.SCENE2); u = pkg.api.uniforms_from_bytes(O.make_uniforms(O.SCENE2, len(prims), 1, 0, width=32, height=16).tobytes()); "
+             "r = pkg.Renderer(32, 16, conv=0); r.upload_scene(prims); r.render_frame(u, pkg.MODE_NONE); print(r.kernel_name())" % root)
+    name = subprocess.run([sys.executable, "-c", probe], env=env, capture_output=True, text=True, timeout=300, cwd=root).stdout
+    assert "trace_native_kernel<CONV, SrcConst, ShapeAny> (strict)" in name, name
