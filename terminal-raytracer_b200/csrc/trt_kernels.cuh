@@ -172,7 +172,7 @@ static __global__ void blend_frames_kernel(float4 *cur, const uint2 *batch, uint
         cur[s] = a;
     }
     accumulation[index] = a;
-    pixels[index] = a;
+    if (pixels != accumulation) pixels[index] = a;
 }
 
 // pack the rows this shard owns contiguously (local row order) for the NCCL gather

@@ -218,11 +218,38 @@ __device__ __forceinline__ void st_release_u64(unsigned long long *p, unsigned l
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// decimal text of a byte, left-aligned: char0 | char1 << 8 | char2 << 16 | digit count << 24 (one table entry per thread)
+__device__ __forceinline__ uint32_t digits_entry(uint32_t v) {
+    const uint32_t h = v / 100u, t = (v / 10u) % 10u, o = v % 10u;
+    if (v >= 100u) return ('0' + h) | (('0' + t) << 8) | (('0' + o) << 16) | (3u << 24);
+    if (v >= 10u) return ('0' + t) | (('0' + o) << 8) | (2u << 24);
+    return ('0' + o) | (1u << 24);
+}
+// branch-free form of put_pixel over the digit table: three characters are always stored, the cursor advances by the
+// digit count, the next store overwrites what was one too many
+__device__ __forceinline__ void put_pixel_lut(uint8_t *d, uint32_t pk, int mode, bool row_end, const uint32_t *dig) {
+    d[0] = 0x1b; d[1] = '['; d[2] = '3'; d[3] = '8'; d[4] = ';'; d[5] = '2'; d[6] = ';';
+    uint32_t n = 7;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const uint32_t e = dig[(pk >> (8 * c)) & 255u];
+        d[n] = (uint8_t)e; d[n + 1] = (uint8_t)(e >> 8); d[n + 2] = (uint8_t)(e >> 16);
+        n += e >> 24;
+        d[n++] = c == 2 ? 'm' : ';';
+    }
+    if (mode == 1) { d[n++] = 0xE2; d[n++] = 0x96; d[n++] = 0x88; }
+    else d[n++] = (uint8_t)c_ramp[pk >> 24];
+    d[n++] = 0x1b; d[n++] = '['; d[n++] = '0'; d[n++] = 'm';
+    if (row_end) { d[n++] = '\r'; d[n++] = '\n'; }
+}
+
 __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q) {
-    __shared__ __align__(16) uint8_t stage[TRT_QF_STAGE];
+    __shared__ __align__(16) uint8_t stage[TRT_QF_STAGE + 4];
+    __shared__ uint32_t s_dig[256];
     __shared__ unsigned int s_tile;
     __shared__ unsigned long long s_base;
     if (threadIdx.x == 0) s_tile = atomicAdd(q.ticket, 1u);
+    s_dig[threadIdx.x & 255u] = digits_entry(threadIdx.x & 255u);
     __syncthreads();
     const unsigned int tile = s_tile;
     const uint64_t n = (uint64_t)q.width * q.height;
@@ -235,7 +262,8 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q)
         if (i0 + j < n) {
             const uint64_t src = q.row_src ? q.row_src[y] + x : i0 + j;
             pk[j] = quantise_pixel(__ldg(&q.src[src]), q.mode);
-            len[j] = pixel_len(pk[j], q.mode, x == q.width - 1u) | (x == 0u ? 0x80000000u : 0u);   // bit 31: first pixel of row y_j
+            const uint32_t nd = (s_dig[pk[j] & 255u] >> 24) + (s_dig[(pk[j] >> 8) & 255u] >> 24) + (s_dig[(pk[j] >> 16) & 255u] >> 24);
+            len[j] = (14u + nd + (q.mode == 1 ? 3u : 1u) + (x == q.width - 1u ? 2u : 0u)) | (x == 0u ? 0x80000000u : 0u);   // bit 31: first pixel of row y_j
             mine += len[j] & 0xffu;
             if (++x == q.width) { x = 0; y++; }
         }
@@ -278,7 +306,7 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q)
     for (int j = 0; j < TRT_QF_PER_THREAD; j++) {
         if (i0 + j < n) {
             if ((len[j] >> 31) && q.row_start) q.row_start[yy] = off + pos;
-            put_pixel(stage + pad + pos, pk[j], q.mode, xx == q.width - 1u);
+            put_pixel_lut(stage + pad + pos, pk[j], q.mode, xx == q.width - 1u, s_dig);
             pos += len[j] & 0xffu;
             if (++xx == q.width) { xx = 0; yy++; }
         }

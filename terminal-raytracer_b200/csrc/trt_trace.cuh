@@ -1085,7 +1085,7 @@ struct Tracer {
         if (fp.frame_number != 0u) a = fp.accumulation[index];
         const float4 out = blend_pixel<CONV>(a, cur, fp.frame_number);
         fp.accumulation[index] = out;
-        fp.pixels[index] = out;
+        if (fp.pixels != fp.accumulation) fp.pixels[index] = out;       // (the library aliases the two: one store)
     }
 };
 
