@@ -155,6 +155,11 @@ extern "C" {
     pub fn trt_multi_read_variance(m: *mut trt_multi, dst: *mut trt_variance, n_pixels: usize) -> c_int;
     pub fn trt_multi_get_frame_stats(m: *mut trt_multi, out: *mut trt_frame_stats) -> c_int;
     pub fn trt_multi_get_timings(m: *mut trt_multi, out: *mut trt_timings) -> c_int;
+    pub fn trt_multi_render_frames(m: *mut trt_multi, u: *const trt_uniforms, n: u32, mode: c_int, out: *mut u8, cap: usize, len: *mut usize) -> c_int;
+    pub fn trt_multi_frames_context(m: *mut trt_multi) -> *mut trt_ctx;
+    pub fn trt_trace_frames_async(ctx: *mut trt_ctx, u: *const trt_uniforms, n: u32) -> c_int;
+    pub fn trt_frame_means(ctx: *mut trt_ctx, dptr: *mut *mut c_void, frame_stride_bytes: *mut usize) -> c_int;
+    pub fn trt_blend_frames_async(ctx: *mut trt_ctx, d_means: *const c_void, u: *const trt_uniforms, n: u32) -> c_int;
     pub fn trt_camera_default(cam: *mut trt_camera);
     pub fn trt_camera_vectors(cam: *const trt_camera, forward: *mut trt_vec3, right: *mut trt_vec3, up: *mut trt_vec3);
     pub fn trt_camera_key(cam: *mut trt_camera, key: c_int) -> c_int;

@@ -250,6 +250,18 @@ int trt_multi_read_pixels(trt_multi *m, float *dst4, size_t n_pixels);
 int trt_multi_read_variance(trt_multi *m, trt_variance *dst, size_t n_pixels);
 int trt_multi_get_frame_stats(trt_multi *m, trt_frame_stats *out);
 int trt_multi_get_timings(trt_multi *m, trt_timings *out);
+/* The second axis (north_star: "by image tiles or by sample batches"): n frames of a still camera -- u[0..n) equal but for
+ * seed and frame_number, as in trt_render_frames -- dealt over the GPUs (frame f on GPU f mod G, one launch per GPU),
+ * their per-frame means gathered on the first GPU and blended there in frame order (shader.wgsl:610-619): accumulation,
+ * pixels, variance and the last frame's stream are bit-identical to n trt_render_frame calls on one GPU.  The result
+ * lives in trt_multi_frames_context(m) (a whole-frame context on the first device). */
+int trt_multi_render_frames(trt_multi *m, const trt_uniforms *u, uint32_t n, int mode, uint8_t *out, size_t cap, size_t *len);
+trt_ctx *trt_multi_frames_context(trt_multi *m);
+/* the two halves of a frame batch on one context: trace n frames into the staging buffer (no blend; means of frame i at
+ * trt_frame_means + i * stride), and blend n means lying in this device's memory into the accumulation, in order */
+int trt_trace_frames_async(trt_ctx *ctx, const trt_uniforms *u, uint32_t n);
+int trt_frame_means(trt_ctx *ctx, void **dptr, size_t *frame_stride_bytes);
+int trt_blend_frames_async(trt_ctx *ctx, const void *d_means, const trt_uniforms *u, uint32_t n);
 
 /* ---- host logic of the reference, restated natively (no GPU needed) --------------------------- */
 

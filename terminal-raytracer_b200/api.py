@@ -149,6 +149,11 @@ SYMBOLS = {
     "trt_multi_read_variance": (C.c_int, [_P, _P, C.c_size_t]),
     "trt_multi_get_frame_stats": (C.c_int, [_P, C.POINTER(FrameStats)]),
     "trt_multi_get_timings": (C.c_int, [_P, C.POINTER(Timings)]),
+    "trt_multi_render_frames": (C.c_int, [_P, C.POINTER(Uniforms), C.c_uint32, C.c_int, _P, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "trt_multi_frames_context": (_P, [_P]),
+    "trt_trace_frames_async": (C.c_int, [_P, C.POINTER(Uniforms), C.c_uint32]),
+    "trt_frame_means": (C.c_int, [_P, C.POINTER(_P), C.POINTER(C.c_size_t)]),
+    "trt_blend_frames_async": (C.c_int, [_P, _P, C.POINTER(Uniforms), C.c_uint32]),
     "trt_camera_default": (None, [C.POINTER(CameraStruct)]),
     "trt_camera_vectors": (None, [C.POINTER(CameraStruct), C.POINTER(Vec3), C.POINTER(Vec3), C.POINTER(Vec3)]),
     "trt_camera_key": (C.c_int, [C.POINTER(CameraStruct), C.c_int]),
@@ -535,6 +540,36 @@ class MultiRenderer:
         n = C.c_size_t()
         self._ck(lib().trt_multi_render_frame(self.h, C.byref(u), mode, self._out[0], cap, C.byref(n)))
         return C.string_at(self._out[0], n.value)
+
+    def render_frames(self, us, mode=MODE_ASCII) -> bytes:
+        """Frames of a still camera dealt over the GPUs (frame f on GPU f mod G), blended in order on the first one;
+        returns the last frame's stream.  `frames_pixels()` / `frames_variance()` read the blended result."""
+        n = len(us)
+        arr = (Uniforms * n)(*us)
+        self.size = (us[0].width, us[0].height)
+        if mode == MODE_NONE:
+            self._ck(lib().trt_multi_render_frames(self.h, arr, n, mode, None, 0, None))
+            return b""
+        cap = us[0].width * us[0].height * 26 + 2 * us[0].height + 64
+        buf = C.create_string_buffer(cap)
+        ln = C.c_size_t()
+        self._ck(lib().trt_multi_render_frames(self.h, arr, n, mode, C.cast(buf, _P), cap, C.byref(ln)))
+        return buf.raw[:ln.value]
+
+    def _frames_read(self, fn, dtype, cols):
+        ctx = lib().trt_multi_frames_context(self.h)
+        w, h = self.size
+        a = np.zeros((w * h, cols), dtype) if cols else np.zeros(w * h, dtype)
+        rc = fn(ctx, a.ctypes.data, w * h)
+        if rc:
+            raise TrtError(rc, lib().trt_last_error(ctx).decode())
+        return a
+
+    def frames_pixels(self):
+        return self._frames_read(lib().trt_read_pixels, np.float32, 4)
+
+    def frames_variance(self):
+        return self._frames_read(lib().trt_read_variance, np.dtype([("variance", "<f4"), ("sample_count", "<u4")]), 0)
 
     def read_pixels(self):
         w, h = self.size

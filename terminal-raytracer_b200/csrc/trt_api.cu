@@ -1157,6 +1157,117 @@ extern "C" int trt_render_frames(trt_ctx *ctx, const trt_uniforms *u, uint32_t n
     return rc;
 }
 
+// ---- frames over GPUs: the two halves of a frame batch as separate calls -----------------------------------
+// trt_trace_frames_async traces n frames of a still camera (one launch, work item = (frame, pixel)) and leaves every
+// frame's per-pixel mean in the context's staging buffer (trt_frame_means), WITHOUT the temporal blend;
+// trt_blend_frames_async applies the blend (shader.wgsl:610-619) in frame order to n means that lie in this device's
+// memory, wherever they were traced.  trt_multi_render_frames deals the frames of a batch over the GPUs (frame f on
+// GPU f mod G), gathers the means on the first GPU and blends them there: bit-identical to one GPU, G times the lanes.
+static int same_but_seed(trt_ctx *ctx, const trt_uniforms *u, uint32_t n, const char *who) {
+    for (uint32_t i = 1; i < n; i++) {
+        trt_uniforms a = u[0], b = u[i];
+        a.seed = b.seed = 0u; a.frame_number = b.frame_number = 0u;
+        if (memcmp(&a, &b, sizeof(trt_uniforms)) != 0) {
+            ctx->err = std::string(who) + ": the frames of a batch may differ only in seed and frame_number";
+            return TRT_ERR_INVALID;
+        }
+    }
+    return TRT_OK;
+}
+
+static int ensure_batch_buffers(trt_ctx *ctx, size_t frames, size_t np, bool means) {
+    if (means && ctx->batch_cur_cap < frames * np) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->d_batch_cur) cudaFree(ctx->d_batch_cur);
+        ctx->d_batch_cur = nullptr; ctx->batch_cur_cap = 0;
+        CK(cudaMalloc(&ctx->d_batch_cur, frames * np * sizeof(float4)));
+        ctx->batch_cur_cap = frames * np;
+    }
+    if (ctx->batch_cap < frames) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        if (ctx->d_batch) cudaFree(ctx->d_batch);
+        ctx->d_batch = nullptr; ctx->batch_cap = 0;
+        CK(cudaMalloc(&ctx->d_batch, frames * sizeof(uint2)));
+        ctx->batch_cap = (uint32_t)frames;
+    }
+    return TRT_OK;
+}
+
+extern "C" int trt_trace_frames_async(trt_ctx *ctx, const trt_uniforms *u, uint32_t n) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (!u || n == 0u) return fail(ctx, TRT_ERR_INVALID, "trace_frames: no frames");
+    int rc = same_but_seed(ctx, u, n, "trace_frames");
+    if (rc) return rc;
+    rc = check_uniforms(ctx, &u[0]);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    rc = ensure_rows(ctx, u[0].width, u[0].height);
+    if (rc) return rc;
+    const size_t np = ctx->rows.size() * (size_t)u[0].width;
+    if (np == 0) return TRT_OK;
+    if ((size_t)n * np * sizeof(float4) > (size_t(6) << 30) || (size_t)n * np > ((size_t(1) << 31) - 1))
+        return fail(ctx, TRT_ERR_INVALID, "trace_frames: the batch does not fit one launch (use trt_render_frames, which chunks)");
+    rc = ensure_batch_buffers(ctx, n, np, true);
+    if (rc) return rc;
+    std::vector<uint2> hb(n);
+    for (uint32_t f = 0; f < n; f++) hb[f] = make_uint2(u[f].seed, u[f].frame_number);
+    CK(cudaMemcpyAsync(ctx->d_batch, hb.data(), n * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));              // hb leaves scope
+    CK(cudaMemsetAsync(ctx->d_stats, 0, TRT_STATS_BYTES, ctx->stream));
+    ctx->launches = 0;
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    rc = trace_impl(ctx, u, n);
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    return TRT_OK;
+}
+
+extern "C" int trt_frame_means(trt_ctx *ctx, void **dptr, size_t *frame_stride_bytes) {
+    if (!ctx || !dptr) return TRT_ERR_INVALID;
+    if (!ctx->d_batch_cur || !ctx->have_frame) return fail(ctx, TRT_ERR_INVALID, "frame_means before trt_trace_frames_async");
+    *dptr = ctx->d_batch_cur;
+    if (frame_stride_bytes) *frame_stride_bytes = ctx->rows.size() * (size_t)ctx->last_u.width * sizeof(float4);
+    return TRT_OK;
+}
+
+extern "C" int trt_blend_frames_async(trt_ctx *ctx, const void *d_means, const trt_uniforms *u, uint32_t n) {
+    if (!ctx) return TRT_ERR_INVALID;
+    if (!d_means || !u || n == 0u) return fail(ctx, TRT_ERR_INVALID, "blend_frames: no frames");
+    int rc = same_but_seed(ctx, u, n, "blend_frames");
+    if (rc) return rc;
+    rc = check_uniforms(ctx, &u[0]);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    rc = ensure_rows(ctx, u[0].width, u[0].height);
+    if (rc) return rc;
+    const size_t np = ctx->rows.size() * (size_t)u[0].width;
+    if (np == 0) return TRT_OK;
+    rc = ensure_batch_buffers(ctx, n, np, false);
+    if (rc) return rc;
+    std::vector<uint2> hb(n);
+    for (uint32_t f = 0; f < n; f++) hb[f] = make_uint2(u[f].seed, u[f].frame_number);
+    CK(cudaMemcpyAsync(ctx->d_batch, hb.data(), n * sizeof(uint2), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const uint32_t *row_map = ctx->cfg.shard_count > 1u ? ctx->d_row_map : nullptr;
+    if (ctx->cfg.conv == 2u) {
+        cudaError_t e = native_blend_launch((float4 *)d_means, ctx->d_batch, n, (uint32_t)np, row_map, u[0].width, ctx->d_accum, ctx->d_pixels,
+                                            ctx->stream);
+        if (e != cudaSuccess) { ctx->err = std::string("blend launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
+    } else if (ctx->cfg.conv == 1u) {
+        blend_frames_kernel<1><<<((uint32_t)np + 255u) / 256u, 256, 0, ctx->stream>>>((float4 *)d_means, ctx->d_batch, n, (uint32_t)np, row_map,
+                                                                                     u[0].width, ctx->d_accum, ctx->d_pixels);
+        CK(cudaGetLastError());
+    } else {
+        blend_frames_kernel<0><<<((uint32_t)np + 255u) / 256u, 256, 0, ctx->stream>>>((float4 *)d_means, ctx->d_batch, n, (uint32_t)np, row_map,
+                                                                                     u[0].width, ctx->d_accum, ctx->d_pixels);
+        CK(cudaGetLastError());
+    }
+    ctx->launches += 1;
+    ctx->last_u = u[n - 1];
+    ctx->have_frame = true;
+    return TRT_OK;
+}
+
 extern "C" const char *trt_trace_kernel_name(const trt_ctx *ctx) { return ctx ? ctx->kernel_name : ""; }
 
 extern "C" int trt_get_timings(trt_ctx *ctx, trt_timings *out) {

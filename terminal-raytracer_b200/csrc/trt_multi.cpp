@@ -13,10 +13,19 @@
 #include <string>
 #include <vector>
 
+#include <cuda_runtime.h>
+
 #include "../../include/trt_b200.h"
 
 struct trt_multi {
     std::vector<trt_ctx *> ctx;
+    // frames over GPUs (trt_multi_render_frames): one whole-frame context per device, created on first use
+    std::vector<trt_ctx *> full;
+    std::vector<int32_t> devices;
+    trt_config cfg{};
+    std::vector<trt_primitive> prims;             // the scene, for contexts created later
+    void *d_gather = nullptr;                     // on devices[0]: the means of all frames of a batch, frame-major
+    size_t gather_cap = 0;
     std::vector<std::vector<uint32_t>> rows;      // rows of every shard at rows_height
     uint32_t rows_height = 0;
     std::vector<uint32_t> len;                    // scratch: one shard's row lengths
@@ -37,6 +46,8 @@ extern "C" const char *trt_multi_last_error(const trt_multi *m) { return m ? m->
 extern "C" void trt_multi_destroy(trt_multi *m) {
     if (!m) return;
     for (trt_ctx *c : m->ctx) trt_destroy(c);
+    for (trt_ctx *c : m->full) trt_destroy(c);
+    if (m->d_gather) { cudaSetDevice(m->devices[0]); cudaFree(m->d_gather); }
     delete m;
 }
 
@@ -60,6 +71,8 @@ extern "C" int trt_multi_create(const int32_t *devices, uint32_t n_devices, cons
         }
         m->ctx.push_back(x);
     }
+    m->devices.assign(devices, devices + n_devices);
+    m->cfg = *cfg;
     *out = m;
     return TRT_OK;
 }
@@ -73,6 +86,11 @@ extern "C" int trt_multi_upload_scene(trt_multi *m, const trt_primitive *prims, 
         const int rc = trt_upload_scene(c, prims, count);
         if (rc != TRT_OK) return cfail(m, rc, c);
     }
+    for (trt_ctx *c : m->full) {
+        const int rc = trt_upload_scene(c, prims, count);
+        if (rc != TRT_OK) return cfail(m, rc, c);
+    }
+    m->prims.assign(prims, prims + count);
     return TRT_OK;
 }
 
@@ -161,3 +179,84 @@ extern "C" int trt_multi_get_timings(trt_multi *m, trt_timings *out) {
     }
     return TRT_OK;
 }
+
+// ---- the second axis: the frames of a still camera over the GPUs -------------------------------------------
+// A pixel's samples cannot be split over GPUs (one serial random-number chain, shader.wgsl:507,517,565), but frames are
+// independent given (seed, frame_number) and meet only in the temporal blend (:610-619), which is per pixel and
+// sequential in the frame index.  GPU g traces frames f = g, g + G, ... as ONE launch each (frame batch), the per-frame
+// means are copied to the first GPU (peer copies over NVLink) and blended there IN FRAME ORDER by the same function a
+// single GPU uses: accumulation, pixels and the byte stream are bit-identical to n trt_render_frame calls on one GPU.
+// This is what fills several GPUs at terminal sizes (C2: 100 frames of 400x200), where row shards are latency-bound.
+extern "C" int trt_multi_render_frames(trt_multi *m, const trt_uniforms *u, uint32_t n, int mode, uint8_t *out, size_t cap, size_t *len) {
+    if (!m || !u || n == 0u) return TRT_ERR_INVALID;
+    if (len) *len = 0;
+    const uint32_t G = (uint32_t)m->devices.size();
+    if (m->full.empty()) {
+        for (uint32_t g = 0; g < G; g++) {
+            trt_config c = m->cfg;
+            c.device = m->devices[g];
+            c.shard_index = 0; c.shard_count = 1; c.stripe_rows = 1;
+            trt_ctx *x = nullptr;
+            int rc = trt_create(&c, &x);
+            if (rc != TRT_OK) return mfail(m, rc, std::string("trt_multi_render_frames: device ") + std::to_string(c.device) + ": " + trt_last_error(nullptr));
+            m->full.push_back(x);
+            rc = trt_upload_scene(x, m->prims.data(), (uint32_t)m->prims.size());
+            if (rc != TRT_OK) return cfail(m, rc, x);
+        }
+    }
+    const size_t np = (size_t)u[0].width * u[0].height;
+    // every GPU's share, queued before anything waits
+    std::vector<std::vector<trt_uniforms>> share(G);
+    for (uint32_t f = 0; f < n; f++) share[f % G].push_back(u[f]);
+    for (uint32_t g = 0; g < G; g++) {
+        if (share[g].empty()) continue;
+        const int rc = trt_trace_frames_async(m->full[g], share[g].data(), (uint32_t)share[g].size());
+        if (rc != TRT_OK) return cfail(m, rc, m->full[g]);
+    }
+    const int root_dev = m->devices[0];
+    if (m->gather_cap < (size_t)n * np * 16) {
+        cudaSetDevice(root_dev);
+        if (m->d_gather) cudaFree(m->d_gather);
+        m->d_gather = nullptr; m->gather_cap = 0;
+        if (cudaMalloc(&m->d_gather, (size_t)n * np * 16) != cudaSuccess) { cudaGetLastError(); return mfail(m, TRT_ERR_NOMEM, "trt_multi_render_frames: gather buffer"); }
+        m->gather_cap = (size_t)n * np * 16;
+    }
+    for (uint32_t g = 0; g < G; g++) {                          // means -> first GPU, into frame order
+        if (share[g].empty()) continue;
+        int rc = trt_sync(m->full[g]);
+        if (rc != TRT_OK) return cfail(m, rc, m->full[g]);
+        void *means = nullptr;
+        size_t stride = 0;
+        rc = trt_frame_means(m->full[g], &means, &stride);
+        if (rc != TRT_OK) return cfail(m, rc, m->full[g]);
+        for (size_t k = 0; k < share[g].size(); k++) {
+            const size_t f = g + k * G;
+            if (cudaMemcpyPeer((char *)m->d_gather + f * np * 16, root_dev, (const char *)means + k * stride, m->devices[g], np * 16) != cudaSuccess) {
+                cudaGetLastError();
+                return mfail(m, TRT_ERR_CUDA, "trt_multi_render_frames: peer copy of a frame's means failed");
+            }
+        }
+    }
+    {   // only the last frame of a sequence leaves its variance behind (shader.wgsl:608 overwrites every frame)
+        const uint32_t gl = (n - 1u) % G;
+        if (gl != 0u) {
+            void *src = nullptr, *dst = nullptr;
+            size_t bytes = 0;
+            if (trt_device_buffer(m->full[gl], 2, &src, &bytes) != TRT_OK || trt_device_buffer(m->full[0], 2, &dst, &bytes) != TRT_OK)
+                return mfail(m, TRT_ERR_INVALID, "trt_multi_render_frames: variance buffers");
+            if (cudaMemcpyPeer(dst, root_dev, src, m->devices[gl], np * sizeof(trt_variance)) != cudaSuccess) { cudaGetLastError(); return mfail(m, TRT_ERR_CUDA, "variance peer copy failed"); }
+        }
+    }
+    int rc = trt_blend_frames_async(m->full[0], m->d_gather, u, n);
+    if (rc != TRT_OK) return cfail(m, rc, m->full[0]);
+    if (mode == TRT_MODE_NONE) { rc = trt_sync(m->full[0]); return rc == TRT_OK ? TRT_OK : cfail(m, rc, m->full[0]); }
+    rc = trt_quantise_async(m->full[0], mode, nullptr);
+    if (rc != TRT_OK) return cfail(m, rc, m->full[0]);
+    size_t nlast = 0;
+    rc = trt_read_stream(m->full[0], out, cap, &nlast);
+    if (len) *len = nlast;
+    return rc == TRT_OK ? TRT_OK : cfail(m, rc, m->full[0]);
+}
+
+// the whole-frame context the blended batch lives in (pixels / accumulation / variance of trt_multi_render_frames)
+extern "C" trt_ctx *trt_multi_frames_context(trt_multi *m) { return m && !m->full.empty() ? m->full[0] : nullptr; }

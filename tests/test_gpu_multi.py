@@ -153,3 +153,32 @@ def test_cli_pipeline_and_gpus_streams_equal_the_serial_loop(pkg, tmp_path):
     assert outs["pipeline"] == outs["serial"]
     assert outs["gpus2"] == outs["serial"]
     assert outs["color_pipeline"] == outs["color"]
+
+
+@pytest.mark.parametrize("conv", [0, 2])
+def test_frames_over_gpus_equal_sequential_frames(pkg, O, conv):
+    """The second axis (C2's shape: frames of a still camera, frame_number = f): frame f on GPU f mod G, means gathered
+    and blended in frame order on the first GPU -- bit-identical to the frames one trt_render_frame call at a time."""
+    prims = O.flatten_scene(O.CORNELL)
+    w, h, n = 100, 50, 11
+    us = [pkg.api.uniforms_from_bytes(O.make_uniforms(O.CORNELL, len(prims), O.c2_seed(f), f, width=w, height=h, spp=16, max_depth=16).tobytes())
+          for f in range(n)]
+    one = pkg.Renderer(w, h, conv=conv)
+    one.upload_scene(prims)
+    for u in us:
+        want = one.render_frame(u, pkg.MODE_TRUECOLOR)
+    want_px, want_var = one.read_pixels(), one.read_variance()
+    one.close()
+    m = pkg.MultiRenderer(w, h, devices(3), conv=conv)
+    m.upload_scene(prims)
+    got = m.render_frames(us, pkg.MODE_TRUECOLOR)
+    assert np.array_equal(bits(m.frames_pixels()), bits(want_px))
+    assert np.array_equal(bits(m.frames_variance()["variance"]), bits(want_var["variance"]))
+    assert got == want
+    if conv == 0:                                        # and against the oracle's own loop
+        acc = None
+        for f in range(n):
+            ref = O.render(prims, O.make_uniforms(O.CORNELL, len(prims), O.c2_seed(f), f, width=w, height=h, spp=16, max_depth=16), accumulation=acc)
+            acc = ref["accumulation"]
+        assert np.array_equal(bits(want_px), bits(ref["pixels"]))
+    m.close()
