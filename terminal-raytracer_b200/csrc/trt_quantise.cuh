@@ -244,7 +244,7 @@ __device__ __forceinline__ void put_pixel_lut(uint8_t *d, uint32_t pk, int mode,
 }
 
 __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q) {
-    __shared__ __align__(16) uint8_t stage[TRT_QF_STAGE + 4];
+    __shared__ __align__(16) uint8_t stage[TRT_QF_STAGE + 32];
     __shared__ uint32_t s_dig[256];
     __shared__ unsigned int s_tile;
     __shared__ unsigned long long s_base;
@@ -270,10 +270,24 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q)
     }
     uint32_t total;
     const uint32_t local = block_exclusive_scan(mine, total);
-    // ---- the tile's offset in the stream: publish the aggregate, look back (warp 0) --------------------------------
+    // publish the tile's byte count at once: successors can look back over it while this tile is still formatting
+    if (threadIdx.x == 0) st_release_u64(&q.tile_state[tile], (tile == 0 ? TRT_QF_FLAG_PFX : TRT_QF_FLAG_AGG) | total);
+    // ---- format the tile's text at its LOCAL offsets (nothing here depends on where the tile lands in the stream) ----
+    {
+        uint32_t pos = local;
+        uint32_t xx = (uint32_t)(i0 - (uint64_t)(i0 / q.width) * q.width);
+#pragma unroll
+        for (int j = 0; j < TRT_QF_PER_THREAD; j++) {
+            if (i0 + j < n) {
+                put_pixel_lut(stage + pos, pk[j], q.mode, xx == q.width - 1u, s_dig);
+                pos += len[j] & 0xffu;
+                if (++xx == q.width) xx = 0;
+            }
+        }
+    }
+    // ---- the tile's offset in the stream: decoupled look-back (warp 0, after its own share of the formatting) --------
     if (threadIdx.x < 32u) {
         const unsigned lane = threadIdx.x;
-        if (lane == 0) st_release_u64(&q.tile_state[tile], (tile == 0 ? TRT_QF_FLAG_PFX : TRT_QF_FLAG_AGG) | total);
         unsigned long long excl = 0;
         int pred = (int)tile - 1;
         while (pred >= 0) {
@@ -296,30 +310,36 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q)
             if (tile == q.n_tiles - 1u) { *q.total = excl + total; if (q.row_start) q.row_start[q.height] = excl + total; }
         }
     }
-    __syncthreads();
+    __syncthreads();                                     // the text is staged and the offset is known
     const uint64_t off = s_base;
     if (off + total > q.out_cap) return;                 // caller checks the length first
-    const uint32_t pad = (uint32_t)((uintptr_t)(q.out + off) & 15u);
-    uint32_t pos = local;
-    uint32_t yy = (uint32_t)(i0 / q.width), xx = (uint32_t)(i0 - (uint64_t)yy * q.width);
+    if (q.row_start) {
+        uint32_t pos = local;
+        uint32_t yy = (uint32_t)(i0 / q.width);
 #pragma unroll
-    for (int j = 0; j < TRT_QF_PER_THREAD; j++) {
-        if (i0 + j < n) {
-            if ((len[j] >> 31) && q.row_start) q.row_start[yy] = off + pos;
-            put_pixel_lut(stage + pad + pos, pk[j], q.mode, xx == q.width - 1u, s_dig);
-            pos += len[j] & 0xffu;
-            if (++xx == q.width) { xx = 0; yy++; }
+        for (int j = 0; j < TRT_QF_PER_THREAD; j++) {
+            if (i0 + j < n) {
+                if (len[j] >> 31) q.row_start[yy] = off + pos;
+                pos += len[j] & 0xffu;
+            }
+            // (row index of pixel j + 1: the row ends where a row-end pixel was just passed)
+            if (i0 + j < n && (uint32_t)((i0 + j) - (uint64_t)yy * q.width) == q.width - 1u) yy++;
         }
     }
-    __syncthreads();
-    uint8_t *dst = q.out + off;                          // dst + k  <->  stage[pad + k]
-    const uint32_t head = min(total, (16u - pad) & 15u); // bytes before the first 16-byte boundary
+    // ---- stage[k] -> dst[k]: 16-byte stores to the 16-byte aligned part of the destination; the staged text sits at an
+    // arbitrary byte phase against it, so every 16 bytes are assembled from five words with funnel shifts ---------------
+    uint8_t *dst = q.out + off;
+    const uint32_t head = min(total, (16u - (uint32_t)((uintptr_t)dst & 15u)) & 15u);     // bytes before the first 16-byte boundary
     const uint32_t body = (total - head) & ~15u;
-    for (uint32_t k = threadIdx.x; k < head; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
-    const uint4 *s4 = reinterpret_cast<const uint4 *>(stage + pad + head);
+    for (uint32_t k = threadIdx.x; k < head; k += TRT_Q_BLOCK) dst[k] = stage[k];
+    const uint32_t sh = (head & 3u) * 8u;
+    const uint32_t *sw = reinterpret_cast<const uint32_t *>(stage + (head & ~3u));
     uint4 *d4 = reinterpret_cast<uint4 *>(dst + head);
-    for (uint32_t k = threadIdx.x; k < body / 16u; k += TRT_Q_BLOCK) d4[k] = s4[k];
-    for (uint32_t k = head + body + threadIdx.x; k < total; k += TRT_Q_BLOCK) dst[k] = stage[pad + k];
+    for (uint32_t k = threadIdx.x; k < body / 16u; k += TRT_Q_BLOCK) {
+        const uint32_t w0 = sw[4u * k], w1 = sw[4u * k + 1u], w2 = sw[4u * k + 2u], w3 = sw[4u * k + 3u], w4 = sw[4u * k + 4u];
+        d4[k] = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+    }
+    for (uint32_t k = head + body + threadIdx.x; k < total; k += TRT_Q_BLOCK) dst[k] = stage[k];
 }
 
 // row lengths from the row starts the fused kernel recorded
