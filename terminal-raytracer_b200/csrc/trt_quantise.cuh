@@ -202,7 +202,12 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_emit_kernel(QuantParams q) 
 // its predecessors' published counts (a warp reads 32 of them at a time), stages the text in shared memory and writes
 // it with 16-byte stores: HBM traffic = 16 B/px in + the stream out, the algorithmic minimum.  The thread that owns the
 // first pixel of a row also records where that row starts (row-addressed streams need every row's length).
+#ifndef TRT_QF_PER_THREAD
 #define TRT_QF_PER_THREAD 4
+#endif
+#ifndef TRT_QF_MIN_CTAS
+#define TRT_QF_MIN_CTAS 1
+#endif
 #define TRT_QF_TILE (TRT_Q_BLOCK * TRT_QF_PER_THREAD)
 #define TRT_QF_STAGE (TRT_QF_TILE * 28 + 32)
 #define TRT_QF_FLAG_AGG (1ull << 62)
@@ -243,7 +248,7 @@ __device__ __forceinline__ void put_pixel_lut(uint8_t *d, uint32_t pk, int mode,
     if (row_end) { d[n++] = '\r'; d[n++] = '\n'; }
 }
 
-__global__ void __launch_bounds__(TRT_Q_BLOCK) quant_fused_kernel(QuantParams q) {
+__global__ void __launch_bounds__(TRT_Q_BLOCK, TRT_QF_MIN_CTAS) quant_fused_kernel(QuantParams q) {
     __shared__ __align__(16) uint8_t stage[TRT_QF_STAGE + 32];
     __shared__ uint32_t s_dig[256];
     __shared__ unsigned int s_tile;
