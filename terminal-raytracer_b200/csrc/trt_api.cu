@@ -14,6 +14,7 @@
 #include "trt_persistent.cuh"
 #include "trt_wave.cuh"
 #include "trt_native.cuh"
+#include "trt_pool.cuh"
 #include "trt_quantise.cuh"
 
 using namespace trt;
@@ -22,6 +23,7 @@ using namespace trt;
 namespace trt {
 cudaError_t native_blend_launch(float4 *cur, const uint2 *batch, uint32_t n_batch, uint32_t n_local_pixels, const uint32_t *row_map,
                                 uint32_t width, float4 *accumulation, float4 *pixels, cudaStream_t stream);
+bool pool_wanted(uint32_t n_work, int sm_count, int ctas_per_sm);      // trt_native.cu
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
                                 cudaStream_t stream, uint32_t *launches, const char **kernel_name);
@@ -41,6 +43,8 @@ static cudaError_t strict_native_launch(int device, const SceneView &sv, const L
         cudaFuncSetAttribute(trace_native_kernel<1, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<0, SrcConst, ShapeCornellStrict>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<1, SrcConst, ShapeCornellStrict>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_pool_kernel<0, SrcConst, ShapeCornellStrict>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_pool_kernel<1, SrcConst, ShapeCornellStrict>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         carveout_set[device] = true;
     }
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
@@ -50,7 +54,13 @@ static cudaError_t strict_native_launch(int device, const SceneView &sv, const L
     if (ctas_env && atoi(ctas_env) >= 1 && atoi(ctas_env) <= TRT_NV_STRICT_CTAS) ctas = (uint32_t)atoi(ctas_env);
     const uint32_t cap = (uint32_t)sm_count * ctas;
     const uint32_t blocks = want < cap ? want : cap;
-    if (constant && cornell) {
+    if (constant && cornell && pool_wanted(n_work, sm_count, TRT_PL_STRICT_CTAS)) {
+        const uint32_t pcap = (uint32_t)sm_count * TRT_PL_STRICT_CTAS;
+        const uint32_t pblocks = want < pcap ? want : pcap;
+        if (conv) trace_pool_kernel<1, SrcConst, ShapeCornellStrict><<<pblocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        else trace_pool_kernel<0, SrcConst, ShapeCornellStrict><<<pblocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+        *name = "trace_pool_kernel<CONV, SrcConst, ShapeCornell> (strict)";
+    } else if (constant && cornell) {
         // the reference's default scene layout: the strict scan with its run list known to the compiler
         if (conv) trace_native_kernel<1, SrcConst, ShapeCornellStrict><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
         else trace_native_kernel<0, SrcConst, ShapeCornellStrict><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
@@ -717,7 +727,7 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
             cudaError_t e = native_trace_launch(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, &ctx->small, fp, ctx->sm_count,
                                                 ctx->stream, &ctx->launches, &ctx->kernel_name);
             if (e != cudaSuccess) { ctx->err = std::string("native trace launch: ") + cudaGetErrorString(e); return TRT_ERR_CUDA; }
-            ctx->cost_kernel = strstr(ctx->kernel_name, "native") || strstr(ctx->kernel_name, "jit");   // the wave fallback records no cost
+            ctx->cost_kernel = strstr(ctx->kernel_name, "native") || strstr(ctx->kernel_name, "jit") || strstr(ctx->kernel_name, "pool");   // the wave fallback records no cost
         } else {
             cudaError_t e = persistent_bind_scene(ctx->device, ctx, ctx->scene_serial, ctx->sv, ctx->lv, ctx->stream);
             // TRT_B200_KERNEL=v1 selects the previous production kernel (A/B measurements only)

@@ -14,11 +14,24 @@
 #include "trt_persistent.cuh"
 #include "trt_wave.cuh"
 #include "trt_native.cuh"
+#include "trt_pool.cuh"
 #include "trt_jit.cuh"
 #include <cstdlib>
 #include <cstring>
 
 namespace trt {
+
+// The chain-pool machine (trt_pool.cuh) pays when the frame holds several pools' worth of pixels: a pixel's wall-clock
+// time grows with chains / lanes, so small frames (bounded by their longest pixel) keep one pixel per lane.
+// TRT_B200_POOL=1 / 0 forces it on (where a pool kernel exists) / off, =auto applies the size rule; unset = off.
+bool pool_wanted(uint32_t n_work, int sm_count, int ctas_per_sm) {
+    static const char *env = getenv("TRT_B200_POOL");
+    if (!env || env[0] == '0') return false;
+    if (env[0] == '1') return true;
+    if (env[0] != 'a') return false;
+    const uint64_t chains = (uint64_t)sm_count * (uint64_t)ctas_per_sm * (TRT_NV_THREADS / 32) * TRT_PL_CHAINS;
+    return (uint64_t)n_work >= 8u * chains;
+}
 
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
@@ -52,6 +65,7 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         cudaFuncSetAttribute(trace_native_kernel<2, SrcConst, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<2, SrcGlobal, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         cudaFuncSetAttribute(trace_native_kernel<2, SrcTiled, ShapeAny>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        cudaFuncSetAttribute(trace_pool_kernel<2, SrcConst, ShapeCornell>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         carveout_set = true;
     }
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
@@ -99,7 +113,11 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         if (e != cudaSuccess) return e;
         name = jk->name.c_str();
     } else if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
-        if (cornell) {
+        if (cornell && pool_wanted(n_work, sm_count, TRT_PL_CTAS_PER_SM)) {
+            const uint32_t pcap = (uint32_t)sm_count * TRT_PL_CTAS_PER_SM;
+            trace_pool_kernel<2, SrcConst, ShapeCornell><<<want < pcap ? want : pcap, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
+            name = "trace_pool_kernel<SrcConst, ShapeCornell>";
+        } else if (cornell) {
             trace_native_kernel<2, SrcConst, ShapeCornell><<<blocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
             name = "trace_native_kernel<SrcConst, ShapeCornell>";
         } else if (constant) {

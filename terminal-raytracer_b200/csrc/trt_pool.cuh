@@ -37,11 +37,10 @@ namespace trt {
 #define TRT_PL_STRICT_CTAS 5
 #endif
 
-enum { PM_ACTIVE = 0, PM_IDLE = 1 };
-// chain record (words; odd stride).  CH_L*: the late sum of the open sample while the chain is live or dead, the
-// direction of the prepared camera ray while it is ready (zeroed when a lane takes it).
-enum { CH_L0, CH_L1, CH_L2,
-       CH_A0, CH_A1, CH_A2,      // dead: the ended sample's radiance (the lane's acc)
+enum { PM_ACTIVE = 0, PM_IDLE = 1, PM_ENDED = 2 };   // ENDED: the path ended in the last iteration, the chain is still the lane's
+// chain record (words; odd stride)
+enum { CH_L0, CH_L1, CH_L2,      // the late sum of the open sample (zeroed by the regeneration pass)
+       CH_A0, CH_A1, CH_A2,      // dead: the ended sample's radiance (the lane's acc); ready: direction of the prepared camera ray
        CH_TAD,                   // dead: the queue's tail when the path ended
        CH_RNG,                   // dead: state the path ended with; ready: state after the camera ray's draws
        CH_PC0, CH_PC1, CH_PC2,   // the pixel's colour sum (:549)
@@ -84,6 +83,7 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
     // warp-uniform state: the queue, the two lists (ring indices < NCH and counts), whether the work list is dry
     uint32_t head = 0, tail = 0;
     uint32_t dhead = 0, dcount = NCH, rhead = 0, rcount = 0;
+    uint32_t closable = NCH;                     // dead chains (a prefix of the list) known to be closable; exact after every queue / regeneration pass
     bool dry = false;
     int sp_k = -1;
     const uint32_t n_work = fp.batch ? fp.n_local_pixels * fp.n_batch : fp.n_local_pixels;
@@ -96,25 +96,33 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
     float3 qsum = f3(0, 0, 0);
     const bool small = !kStrict && (SHAPE::kFixed || (SRC::kSmall && c_small.ok));
 
+    // The dead list is in order of death and the queue is a FIFO, so the closable chains -- those whose light samples
+    // are resolved: head has passed the queue's tail at their death -- are a prefix of the list (counted up to 32).
+    auto count_closable = [&]() {
+        const uint32_t n = dcount < 32u ? dcount : 32u;
+        bool ok = false;
+        if (lane < n) {
+            uint32_t pos = dhead + lane;
+            if (pos >= NCH) pos -= NCH;
+            ok = (int)(head - lds_u(TRT_CH(dead[pos], CH_TAD))) >= 0;
+        }
+        const unsigned okm = __ballot_sync(0xffffffffu, ok);
+        closable = okm == 0xffffffffu ? 32u : (uint32_t)__ffs((int)~okm) - 1u;
+    };
+
     for (;;) {
         // ---- regeneration passes: close the ended samples of up to 32 dead chains, finish / hand out pixels, prepare
         // the next camera rays (shader.wgsl:548-565, :596-621, :507-546) -------------------------------------------
-        unsigned m_idle = __ballot_sync(0xffffffffu, mode == PM_IDLE);
-        while (dcount != 0u && (dcount >= (dry ? 1u : 32u) || (uint32_t)__popc(m_idle) > rcount)) {
-            const uint32_t n = dcount < 32u ? dcount : 32u;
+        const unsigned m_na = __ballot_sync(0xffffffffu, mode != PM_ACTIVE);     // lanes without a ray
+        while (closable >= (dry ? 1u : 32u) || (closable != 0u && (uint32_t)__popc(m_na) > rcount)) {
+            const uint32_t n_in = closable < 32u ? closable : 32u;
             unsigned c = 0;
-            bool ok = false;
-            if (lane < n) {
+            if (lane < n_in) {
                 uint32_t pos = dhead + lane;
                 if (pos >= NCH) pos -= NCH;
                 c = dead[pos];
-                ok = (int)(head - lds_u(TRT_CH(c, CH_TAD))) >= 0;      // its light samples are resolved (FIFO queue)
             }
-            // the dead list is in order of death, so the closable chains are a prefix of it
-            const unsigned okm = __ballot_sync(0xffffffffu, ok);
-            const uint32_t closable = okm == 0xffffffffu ? 32u : (uint32_t)__ffs((int)~okm) - 1u;
-            if (!(closable >= (dry ? 1u : 32u) || (closable != 0u && (uint32_t)__popc(m_idle) > rcount))) break;
-            const bool in = lane < closable;
+            const bool in = lane < n_in;
             float3 pc = f3(0, 0, 0), sq = f3(0, 0, 0);
             uint32_t xy = 0, si = 0, tgt = CHF_NEW, crng = 0, fslot = 0, nb = 0;
             bool need_pixel = false, cont = false;
@@ -205,7 +213,8 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
                 crng = pcg_hash(crng + si * 5096u);
                 float3 o, d;
                 tr.camera_ray(crng, xy & 0xffffu, xy >> 16, o, d);
-                sts_f(TRT_CH(c, CH_L0), d.x); sts_f(TRT_CH(c, CH_L1), d.y); sts_f(TRT_CH(c, CH_L2), d.z);
+                sts_f(TRT_CH(c, CH_A0), d.x); sts_f(TRT_CH(c, CH_A1), d.y); sts_f(TRT_CH(c, CH_A2), d.z);
+                sts_f(TRT_CH(c, CH_L0), 0.0f); sts_f(TRT_CH(c, CH_L1), 0.0f); sts_f(TRT_CH(c, CH_L2), 0.0f);
                 sts_u(TRT_CH(c, CH_RNG), crng);
                 sts_f(TRT_CH(c, CH_PC0), pc.x); sts_f(TRT_CH(c, CH_PC1), pc.y); sts_f(TRT_CH(c, CH_PC2), pc.z);
                 sts_f(TRT_CH(c, CH_SQ0), sq.x); sts_f(TRT_CH(c, CH_SQ1), sq.y); sts_f(TRT_CH(c, CH_SQ2), sq.z);
@@ -220,21 +229,35 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
                 ready[pos] = (unsigned char)c;
             }
             rcount += (uint32_t)__popc(m_cont);
-            dhead += closable;
+            dhead += n_in;
             if (dhead >= NCH) dhead -= NCH;
-            dcount -= closable;
+            dcount -= n_in;
             __syncwarp();
+            count_closable();
         }
 
-        // ---- idle lanes take ready chains -----------------------------------------------------------------------
-        if (m_idle != 0u && rcount != 0u) {
-            const uint32_t k = (uint32_t)__popc(m_idle & lt_mask);
+        // ---- lanes without a ray: an ended path's chain joins the dead list, the lane takes a ready chain -----------
+        if (m_na != 0u) {
+            const unsigned m_end = __ballot_sync(0xffffffffu, mode == PM_ENDED);
+            if (mode == PM_ENDED) {
+                uint32_t pos = dhead + dcount + (uint32_t)__popc(m_end & lt_mask);
+                if (pos >= NCH) pos -= NCH;
+                if (pos >= NCH) pos -= NCH;
+                dead[pos] = (unsigned char)cid;
+                sts_f(TRT_CH(cid, CH_A0), acc.x); sts_f(TRT_CH(cid, CH_A1), acc.y); sts_f(TRT_CH(cid, CH_A2), acc.z);
+                sts_u(TRT_CH(cid, CH_RNG), rng);
+                sts_u(TRT_CH(cid, CH_TAD), tail);                 // closable once the queue's head has passed this point
+                red_u(TRT_CH(cid, CH_NB), tr.n_bounces - nb0);
+                mode = PM_IDLE;
+            }
+            dcount += (uint32_t)__popc(m_end);
+            if (tail == head) closable = dcount;                  // with an empty queue a chain is closable the moment it dies
+            const uint32_t k = (uint32_t)__popc(m_na & lt_mask);
             if (mode == PM_IDLE && k < rcount) {
                 uint32_t pos = rhead + k;
                 if (pos >= NCH) pos -= NCH;
                 cid = ready[pos];
-                rd = f3(lds_f(TRT_CH(cid, CH_L0)), lds_f(TRT_CH(cid, CH_L1)), lds_f(TRT_CH(cid, CH_L2)));
-                sts_f(TRT_CH(cid, CH_L0), 0.0f); sts_f(TRT_CH(cid, CH_L1), 0.0f); sts_f(TRT_CH(cid, CH_L2), 0.0f);
+                rd = f3(lds_f(TRT_CH(cid, CH_A0)), lds_f(TRT_CH(cid, CH_A1)), lds_f(TRT_CH(cid, CH_A2)));
                 rng = lds_u(TRT_CH(cid, CH_RNG));
                 ro = fp.cam_pos;                                       // camera_ray: every ray starts at the eye (:546)
                 att = f3(1.0f, 1.0f, 1.0f);
@@ -243,7 +266,7 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
                 nb0 = tr.n_bounces;
                 mode = PM_ACTIVE;
             }
-            const uint32_t take = (uint32_t)__popc(m_idle) < rcount ? (uint32_t)__popc(m_idle) : rcount;
+            const uint32_t take = (uint32_t)__popc(m_na) < rcount ? (uint32_t)__popc(m_na) : rcount;
             rhead += take;
             if (rhead >= NCH) rhead -= NCH;
             rcount -= take;
@@ -264,7 +287,7 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
         {
             const uint32_t cnt = tail - head;
             if (sp_k < 0 && cnt > 0u) {
-                if (cnt >= 32u || cnt + TRT_NV_WAIT_W * (32u - (uint32_t)__popc(m_active)) >= 32u || !m_active) { sp_k = 0; qsum = f3(0, 0, 0); }
+                if (cnt >= 32u || cnt + TRT_NV_WAIT_W * (uint32_t)__popc(~m_active) >= 32u || !m_active) { sp_k = 0; qsum = f3(0, 0, 0); }
             }
             spass = sp_k >= 0;
             qn = cnt < 32u ? cnt : 32u;
@@ -324,6 +347,7 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
                 ordered_late_add<CONV>(qvalid && any, qowner, TRT_CH(qowner, CH_L0), E, EA, qsum);
                 sp_k = -1;
                 head += qn;
+                count_closable();
             }
             __syncwarp();
             continue;
@@ -413,22 +437,7 @@ __device__ __forceinline__ void trace_pool_body(const SceneView &sc, const Light
             if (depth >= fp.max_depth) path_end = true;
         }
 
-        // ---- a path that has ended: its chain joins the dead list, the lane is free ---------------------------------
-        const unsigned m_end = __ballot_sync(0xffffffffu, path_end);
-        if (m_end) {
-            if (path_end) {
-                uint32_t pos = dhead + dcount + (uint32_t)__popc(m_end & lt_mask);
-                if (pos >= NCH) pos -= NCH;
-                if (pos >= NCH) pos -= NCH;
-                dead[pos] = (unsigned char)cid;
-                sts_f(TRT_CH(cid, CH_A0), acc.x); sts_f(TRT_CH(cid, CH_A1), acc.y); sts_f(TRT_CH(cid, CH_A2), acc.z);
-                sts_u(TRT_CH(cid, CH_RNG), rng);
-                sts_u(TRT_CH(cid, CH_TAD), tail);                 // closable once the queue's head has passed this point
-                red_u(TRT_CH(cid, CH_NB), tr.n_bounces - nb0);
-                mode = PM_IDLE;
-            }
-            dcount += (uint32_t)__popc(m_end);
-        }
+        if (path_end) mode = PM_ENDED;                           // its chain is handed in at the top of the loop
         __syncwarp();
     }
     tr.flush_stats();
