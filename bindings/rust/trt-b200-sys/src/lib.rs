@@ -135,6 +135,9 @@ extern "C" {
     pub fn trt_pack_shard_pixels(ctx: *mut trt_ctx, d_dst: *mut c_void, dst_bytes: usize) -> c_int;
     pub fn trt_quantise_gathered(ctx: *mut trt_ctx, d_gathered: *const c_void, block_stride_bytes: usize, width: u32, height: u32,
                                  shard_count: u32, stripe_rows: u32, mode: c_int, len_needed_or_null: *mut usize) -> c_int;
+    /// allocates nothing: static device scratch, frames up to TRT_NOALLOC_MAX_PIXELS (no counterpart in the reference)
+    pub fn trt_quantise_noalloc(device: c_int, d_pixels: *const c_void, width: u32, height: u32, mode: c_int, d_out: *mut c_void,
+                                out_cap: usize, d_len: *mut c_void, cuda_stream: *mut c_void, err: *mut c_char, err_cap: usize) -> c_int;
     pub fn trt_alloc_host(bytes: usize, out: *mut *mut c_void) -> c_int;
     pub fn trt_free_host(p: *mut c_void);
     pub fn trt_host_register(p: *mut c_void, bytes: usize) -> c_int;

@@ -209,6 +209,23 @@ int trt_quantise_gathered(trt_ctx *ctx, const void *d_gathered, size_t block_str
                           uint32_t width, uint32_t height, uint32_t shard_count, uint32_t stripe_rows,
                           int mode, size_t *len_needed_or_null);
 
+/* Quantiser that ALLOCATES NOTHING.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernel and same bytes as trt_quantise_async / trt_render_frame (lib.rs:503-532 on the device); the kernel's
+ * scratch (tile ticket, look-back states, stream length) is a static device array of TRT_NOALLOC_SCRATCH_BYTES that
+ * every GPU holds from the moment it loads the library until exit.  d_pixels: width x height float4 pixels, row-major,
+ * device memory, 16-byte aligned; d_out: device buffer of out_cap bytes for the stream (width * height * 26 + 2 *
+ * height bytes always suffice; a stream longer than out_cap is not written, *d_len still tells its size); d_len: device
+ * uint64_t, receives the stream's length.  Asynchronous on `cuda_stream` (a cudaStream_t, NULL = the default stream);
+ * no context, no cudaMalloc / cudaFree, no host synchronisation.  The first call per device looks the array's address
+ * up (make that call outside a graph capture).  Frames of more than TRT_NOALLOC_MAX_PIXELS pixels are rejected with
+ * TRT_ERR_INVALID and a text in `err` (NULL allowed).  All calls on a device share the array: calls that overlap on
+ * the GPU (different streams without a dependency between them) race -- serialise them. */
+#define TRT_NOALLOC_MAX_PIXELS    8388608u   /* 8192 tiles of 1024 pixels; a 3840x2160 frame (8 294 400) fits */
+#define TRT_NOALLOC_SCRATCH_BYTES 65792u
+int trt_quantise_noalloc(int device, const void *d_pixels, uint32_t width, uint32_t height, int mode, void *d_out,
+                         size_t out_cap, void *d_len, void *cuda_stream, char *err, size_t err_cap);
+
 /* pinned host memory for `out` buffers (optional; any host pointer works) */
 int trt_alloc_host(size_t bytes, void **out);
 void trt_free_host(void *p);

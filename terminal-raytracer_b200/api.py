@@ -102,6 +102,7 @@ assert C.sizeof(Vec3) == 16 and C.sizeof(Primitive) == 180 and C.sizeof(Uniforms
 _P = C.c_void_p
 SYMBOLS = {
     "trt_create": (C.c_int, [C.POINTER(Config), C.POINTER(_P)]),
+    "trt_quantise_noalloc": (C.c_int, [C.c_int, _P, C.c_uint32, C.c_uint32, C.c_int, _P, C.c_size_t, _P, _P, C.c_char_p, C.c_size_t]),
     "trt_destroy": (None, [_P]),
     "trt_last_error": (C.c_char_p, [_P]),
     "trt_upload_scene": (C.c_int, [_P, _P, C.c_uint32]),
