@@ -23,7 +23,7 @@ using namespace trt;
 namespace trt {
 cudaError_t native_blend_launch(float4 *cur, const uint2 *batch, uint32_t n_batch, uint32_t n_local_pixels, const uint32_t *row_map,
                                 uint32_t width, float4 *accumulation, float4 *pixels, cudaStream_t stream);
-bool pool_wanted(uint32_t n_work, int sm_count, int ctas_per_sm);      // trt_native.cu
+bool pool_wanted(uint32_t n_work, int sm_count, int ctas_per_sm, bool strict);      // trt_native.cu
 cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long long serial, const SceneView &sv,
                                 const LightView &lv, const SmallScene *small, const FrameParams &fp, int sm_count,
                                 cudaStream_t stream, uint32_t *launches, const char **kernel_name);
@@ -54,7 +54,7 @@ static cudaError_t strict_native_launch(int device, const SceneView &sv, const L
     if (ctas_env && atoi(ctas_env) >= 1 && atoi(ctas_env) <= TRT_NV_STRICT_CTAS) ctas = (uint32_t)atoi(ctas_env);
     const uint32_t cap = (uint32_t)sm_count * ctas;
     const uint32_t blocks = want < cap ? want : cap;
-    if (constant && cornell && pool_wanted(n_work, sm_count, TRT_PL_STRICT_CTAS)) {
+    if (constant && cornell && pool_wanted(n_work, sm_count, TRT_PL_STRICT_CTAS, true)) {
         const uint32_t pcap = (uint32_t)sm_count * TRT_PL_STRICT_CTAS;
         const uint32_t pblocks = want < pcap ? want : pcap;
         if (conv) trace_pool_kernel<1, SrcConst, ShapeCornellStrict><<<pblocks, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);

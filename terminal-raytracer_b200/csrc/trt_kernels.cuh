@@ -38,7 +38,8 @@ __global__ void repack_kernel(RepackParams rp) {
         } else if (p.primitive_type == 2u) {
             float3 e1 = V::sub(ld3(p.triangle_v1), ld3(p.triangle_v0));
             float3 e2 = V::sub(ld3(p.triangle_v2), ld3(p.triangle_v0));
-            a = f4(ld3(p.triangle_v0), 0.0f);
+            // .w: squared radius of a sphere around v0 that holds the triangle, 10 % to spare (scan_run's cull, conv 2)
+            a = f4(ld3(p.triangle_v0), 1.21f * fmaxf(V::dot(e1, e1), V::dot(e2, e2)));
             b = f4(e1, 0.0f);
             c = f4(e2, 0.0f);
             n = f4(V::normalize(V::cross(e1, e2)), 0.0f);

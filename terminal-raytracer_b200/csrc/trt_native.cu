@@ -21,14 +21,16 @@
 
 namespace trt {
 
-// The chain-pool machine (trt_pool.cuh) pays when the frame holds several pools' worth of pixels: a pixel's wall-clock
-// time grows with chains / lanes, so small frames (bounded by their longest pixel) keep one pixel per lane.
-// TRT_B200_POOL=1 / 0 forces it on (where a pool kernel exists) / off, =auto applies the size rule; unset = off.
-bool pool_wanted(uint32_t n_work, int sm_count, int ctas_per_sm) {
+// The chain-pool machine (trt_pool.cuh).  A pixel's wall-clock time grows with chains / lanes, so only frames that hold
+// several pools' worth of pixels may use it (small frames are bounded by their longest pixel).  Measured on B200
+// (profiles/r2_ab_pool.txt, C3): strict builds +3.4 % (2 412 -> 2 495 Msamples/s) -- on by default there; conv 2 -0.9 %
+// (it needs 72 registers, i.e. 7 resident CTAs instead of 8) -- off by default.  TRT_B200_POOL=1 / 0 forces it on
+// (wherever a pool kernel exists, whatever the frame size) / off; =auto applies the size rule to both.
+bool pool_wanted(uint32_t n_work, int sm_count, int ctas_per_sm, bool strict) {
     static const char *env = getenv("TRT_B200_POOL");
-    if (!env || env[0] == '0') return false;
-    if (env[0] == '1') return true;
-    if (env[0] != 'a') return false;
+    if (env && env[0] == '0') return false;
+    if (env && env[0] == '1') return true;
+    if (!strict && !(env && env[0] == 'a')) return false;
     const uint64_t chains = (uint64_t)sm_count * (uint64_t)ctas_per_sm * (TRT_NV_THREADS / 32) * TRT_PL_CHAINS;
     return (uint64_t)n_work >= 8u * chains;
 }
@@ -113,7 +115,7 @@ cudaError_t native_trace_launch(int device, const void *ctx_key, unsigned long l
         if (e != cudaSuccess) return e;
         name = jk->name.c_str();
     } else if (!force_wave && sv.n_lights <= TRT_NV_MAX_LIGHTS) {
-        if (cornell && pool_wanted(n_work, sm_count, TRT_PL_CTAS_PER_SM)) {
+        if (cornell && pool_wanted(n_work, sm_count, TRT_PL_CTAS_PER_SM, false)) {
             const uint32_t pcap = (uint32_t)sm_count * TRT_PL_CTAS_PER_SM;
             trace_pool_kernel<2, SrcConst, ShapeCornell><<<want < pcap ? want : pcap, TRT_NV_THREADS, 0, stream>>>(sv, lv, fp);
             name = "trace_pool_kernel<SrcConst, ShapeCornell>";

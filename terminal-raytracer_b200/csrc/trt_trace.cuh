@@ -152,10 +152,13 @@ struct SrcGrid : SrcGlobal {
     static constexpr bool kGrid = true;
     __device__ SrcGrid(const SceneView &s, const LightView &l) : SrcGlobal(s, l) {}
 };
+#ifndef TRT_TILED_CTAS
+#define TRT_TILED_CTAS 6
+#endif
 struct SrcTiled : SrcGlobal {
     static constexpr bool kTiled = true;
     static constexpr int kTileSlots = 2 * 3 * TRT_TILE;      // two buffers of (ga, gb, gc)[TRT_TILE]
-    static constexpr int kCtasPerSm = 6;                     // 80 registers: the scan loop must not spill
+    static constexpr int kCtasPerSm = TRT_TILED_CTAS;        // 6: 80 registers; the scan loop must not spill
     __device__ SrcTiled(const SceneView &s, const LightView &l) : SrcGlobal(s, l) {}
 };
 // geometry accessor over one staged tile: index i is the primitive's scan-order index
@@ -220,6 +223,11 @@ __device__ __forceinline__ float dotz(float3 a, float3 b, bool z0, bool z1, bool
 #endif
 #ifndef TRT_V_NO_RENORM
 #define TRT_V_NO_RENORM 1
+#endif
+// TRT_V_TRI_CULL: triangle runs of 8 or more in the run-loop scans (scan_run: SrcTiled / SrcGlobal / unspecialised
+// scenes, conv 2) test the ray against a sphere around v0 first.  0 = every triangle takes the full test (round 1, A/B).
+#ifndef TRT_V_TRI_CULL
+#define TRT_V_TRI_CULL 1
 #endif
 
 template <int CONV, bool COUNT, class SRC>
@@ -515,22 +523,44 @@ struct Tracer {
                     if (fabsf(denom) >= 0.0001f && t >= t_min && t < closest) { closest = t; best = i; }
                 }
             } else if (run.x == 2) {
-#pragma unroll UNROLL
-                for (int i = run.y; i < run.z; i++) {
+                // hit_triangle (shader.wgsl:192-223) for one triangle, as written in this convention
+                auto full = [&](int i) {
                     const float3 e1 = xyz(acc.gb(i)), e2 = xyz(acc.gc(i));
                     const float3 h = V::cross(rd, e2);
                     const float a = V::dot(e1, h);
-                    if (a > -0.00001f && a < 0.00001f) continue;
+                    if (a > -0.00001f && a < 0.00001f) return;
                     const float f = rcp_native(a);
                     const float3 s = V::sub(ro, xyz(acc.ga(i)));
                     const float u = f * V::dot(s, h);
-                    if (u < 0.0f || u > 1.0f) continue;
+                    if (u < 0.0f || u > 1.0f) return;
                     const float3 q = V::cross(s, e1);
                     const float v = f * V::dot(rd, q);
-                    if (v < 0.0f || u + v > 1.0f) continue;
+                    if (v < 0.0f || u + v > 1.0f) return;
                     const float t = f * V::dot(e2, q);
                     if (t > t_min && t < closest) { closest = t; best = i; }
+                };
+                int i = run.y;
+#if TRT_V_TRI_CULL
+                // Long runs (the tiled / global scans of a large scene): a conservative cull in front of the test.  A ray
+                // that hits the triangle passes within r = max(|e1|, |e2|) of v0, so when its LINE stays further away
+                // than that the as-written test would reject it too (u or v outside [0, 1]).  One 16-byte load (v0 and
+                // r^2 in ga.w, written by repack_kernel with 10 % to spare) and 12 arithmetic instructions instead of
+                // three loads and ~25; d2 = |tc|^2 - (tc . d)^2 is as exact as |tc|^2 * 1e-6 (|d| = 1 to a few ulp,
+                // cancellation), hence the second term.  Survivors run the test as written: accepted hits are unchanged.
+                if (run.z - run.y >= 8) {
+#pragma unroll UNROLL
+                    for (; i < run.z; i++) {
+                        const float4 v0r = acc.ga(i);
+                        const float3 tc = V::sub(xyz(v0r), ro);
+                        const float t_ca = V::dot(tc, rd);
+                        const float tcc = V::dot(tc, tc);
+                        if (V::nmadd(tcc, t_ca, t_ca) > __fmaf_rn(2e-5f, tcc, v0r.w)) continue;
+                        full(i);
+                    }
                 }
+#endif
+#pragma unroll UNROLL
+                for (; i < run.z; i++) full(i);
             }
     }
 

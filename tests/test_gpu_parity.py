@@ -233,3 +233,24 @@ def test_deferred_machine_is_bit_exact_on_every_scene(tmp_path):
              "r = pkg.Renderer(32, 16, conv=0); r.upload_scene(prims); r.render_frame(u, pkg.MODE_NONE); print(r.kernel_name())" % root)
     name = subprocess.run([sys.executable, "-c", probe], env=env, capture_output=True, text=True, timeout=300, cwd=root).stdout
     assert "trace_native_kernel<CONV, SrcConst, ShapeAny> (strict)" in name, name
+
+
+def test_chain_pool_machine_is_bit_exact(tmp_path):
+    """trace_pool_kernel (trt_pool.cuh: a pool of pixel chains per warp, regeneration at SIMT width) serves strict frames
+    that hold several pools' worth of pixels (C3; checked there inside the bench run, config.parity).  Here it is forced
+    onto the small frames of the strict tests and of the named configurations: TRT_B200_POOL=1."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, TRT_B200_POOL="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-x",
+                        os.path.join(root, "tests", "test_gpu_parity.py"), os.path.join(root, "tests", "test_golden.py"),
+                        os.path.join(root, "tests", "test_gpu_batch.py"), os.path.join(root, "tests", "test_gpu_named_configs.py"),
+                        "-k", "not deferred_machine and not chain_pool and not c5_all and not c4_full"],
+                       env=env, capture_output=True, text=True, timeout=900, cwd=root)
+    assert r.returncode == 0, r.stdout[-3000:]
+    probe = ("import json,os,sys; sys.path.insert(0, %r); import __graft_entry__ as g; pkg, O = g.load_package(), g.load_oracle(); "
+             "prims = O.flatten_scene(O.CORNELL); u = pkg.api.uniforms_from_bytes(O.make_uniforms(O.CORNELL, len(prims), 1, 0, width=32, height=16).tobytes()); "
+             "r = pkg.Renderer(32, 16, conv=0); r.upload_scene(prims); r.render_frame(u, pkg.MODE_NONE); print(r.kernel_name())" % root)
+    name = subprocess.run([sys.executable, "-c", probe], env=env, capture_output=True, text=True, timeout=300, cwd=root).stdout
+    assert "trace_pool_kernel<CONV, SrcConst, ShapeCornell> (strict)" in name, name

@@ -18,5 +18,6 @@ for f in range(2):
     r.render_frame(pkg.api.uniforms_from_bytes(u.tobytes()), pkg.MODE_TRUECOLOR)
 t, st = r.timings(), r.frame_stats()
 print(f"{scene} {w}x{h} spp {spp} conv {conv}: trace {t.trace_ms:.3f} ms quantise {t.quantise_ms:.3f} ms d2h {t.d2h_ms:.3f} ms; "
-      f"{st.samples_traced} samples, {st.bounces} bounces -> {st.samples_traced / t.trace_ms / 1e3:.1f} Msamples/s")
+      f"{st.samples_traced} samples, {st.bounces} bounces -> {st.samples_traced / t.trace_ms / 1e3:.1f} Msamples/s; "
+      f"pixels sha1 {__import__('hashlib').sha1(r.read_pixels().tobytes()).hexdigest()[:12]}")
 r.close()
