@@ -397,6 +397,11 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
     std::vector<int4> tiles;
     for (const int4 &r : runs)
         for (int t0 = r.y; t0 < r.z; t0 += TRT_TILE) tiles.push_back(make_int4(r.x, t0, std::min(TRT_TILE, r.z - t0), 0));
+    {   // triangle and sphere tiles: where their pair-packed cull entries start in gd (two entries per pair of primitives)
+        int next = 0;
+        for (int4 &t : tiles)
+            if (t.x == 2 || t.x == 0) { t.w = next; next += 2 * ((t.z + 1) / 2); }
+    }
     const uint32_t n_lights = (uint32_t)light_prim.size(), n_runs = (uint32_t)runs.size();
     CK(cudaStreamSynchronize(ctx->stream));
     if (count > ctx->cap_prims) {
@@ -404,7 +409,7 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
         ctx->d_aos = nullptr; ctx->d_geom = nullptr; ctx->d_type = nullptr; ctx->cap_prims = 0;
         const uint32_t cap = count < 64u ? 64u : count;
         CK(cudaMalloc(&ctx->d_aos, (size_t)cap * sizeof(trt_primitive)));
-        CK(cudaMalloc(&ctx->d_geom, (size_t)cap * 6 * sizeof(float4)));
+        CK(cudaMalloc(&ctx->d_geom, (size_t)cap * 8 * sizeof(float4)));     // ga gb gc gn mc me + gd (<= count + tiles entries)
         CK(cudaMalloc(&ctx->d_type, cap));
         ctx->cap_prims = cap;
     }
@@ -455,9 +460,14 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
         else repack_kernel<0><<<(work + 127) / 128, 128, 0, ctx->stream>>>(rp);
         CK(cudaGetLastError());
     }
+    if (!tiles.empty() && count) {
+        pack_cull_kernel<<<(unsigned)tiles.size(), 64, 0, ctx->stream>>>(rp.ga, ctx->d_tiles, (int)tiles.size(), ctx->d_geom + 6 * cp);
+        CK(cudaGetLastError());
+    }
     for (const PairInfo &pi : pairs)
         CK(cudaMemcpyAsync(rp.gc + pi.index, &pi.v, sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     ctx->sv.ga = rp.ga; ctx->sv.gb = rp.gb; ctx->sv.gc = rp.gc; ctx->sv.gn = rp.gn; ctx->sv.mc = rp.mc; ctx->sv.me = rp.me;
+    ctx->sv.gd = ctx->d_geom + 6 * cp;
     ctx->sv.type = ctx->d_type; ctx->sv.runs = ctx->d_runs; ctx->sv.lights = ctx->d_lights;
     ctx->sv.n_prims = (int)count; ctx->sv.n_runs = (int)n_runs; ctx->sv.n_lights = (int)n_lights;
     ctx->sv.tiles = ctx->d_tiles; ctx->sv.n_tiles = (int)tiles.size();

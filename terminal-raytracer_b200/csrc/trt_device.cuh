@@ -32,11 +32,15 @@ namespace trt {
 // sequence the shader uses, so it is bit-identical to recomputing it per test.
 struct SceneView {
     const float4 *ga, *gb, *gc, *gn, *mc, *me;
+    // triangle and sphere tiles of the cooperative scan, two primitives per entry pair: (x_a, x_b, y_a, y_b), (z_a, z_b,
+    // -R_a, -R_b) with (x, y, z) = v0 / the centre and R = ga.w / r^2 (the cull of scan_run on packed FP32 pairs); a
+    // tile's entries start at tiles[k].w
+    const float4 *gd;
     const uint8_t *type;        // per primitive: 0 sphere, 1 plane, 2 triangle, 255 unknown
     const int4 *runs;           // (type, begin, end, -) maximal runs of equal type, in scan order
     const int4 *lights;         // (prim index, type, area as float bits, -) emissive spheres/triangles in scan order
     int n_prims, n_runs, n_lights;
-    // tiles of at most TRT_TILE consecutive primitives of one run, in scan order: (type, first index, count, -);
+    // tiles of at most TRT_TILE consecutive primitives of one run, in scan order: (type, first index, count, first gd entry);
     // the CTA-cooperative scan of large scenes stages one tile at a time in shared memory (trt_trace.cuh)
     const int4 *tiles;
     int n_tiles;
@@ -49,7 +53,7 @@ struct SceneView {
     int gx, gy, gz;
     float3 grid_min, grid_cell, grid_inv_cell;
 };
-#define TRT_TILE 128
+#define TRT_TILE 96             // x 4 arrays (ga, gb, gc, gd) x 2 buffers x 16 B = 12 KB of shared memory per CTA
 
 #define TRT_CONST_PRIMS 256     // scenes up to this size are also mirrored in __constant__ memory
 
@@ -143,6 +147,15 @@ __device__ __forceinline__ float3 div3_rn(float3 a, float s) {
 // and allows fused multiply-add everywhere; conv 2 uses the SM's native units within those bounds:
 // MUFU.RCP / RSQ / SQRT / SIN / COS (1-2 ulp) and FFMA contraction (this convention is only
 // instantiated in trt_native.cu, which is compiled with --fmad=true -use_fast_math).
+// Packed FP32 pairs (sm_100: add / mul / fma .f32x2 -> FADD2 / FMUL2 / FFMA2, two IEEE operations per issue slot; the FMA
+// pipe needs two cycles for them, so the FLOP rate is that of the scalar forms -- measured 73.4 against 70.9 TFLOP/s,
+// tools/micro/ffma2_rate.cu -- but a kernel bound by ISSUE slots gets the second operation for free).
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float lo, float hi) { f2_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void f2_unpack(f2_t v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) { f2_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 __device__ __forceinline__ float rcp_native(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float rsqrt_native(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float sqrt_native(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }

@@ -71,6 +71,27 @@ __global__ void repack_kernel(RepackParams rp) {
     }
 }
 
+// Cull data of the triangle and sphere tiles, two primitives per entry pair (SceneView::gd): one block per tile.
+// Per primitive a point and a squared distance R such that a ray whose line stays further from the point than that
+// cannot hit: triangle (v0, ga.w); sphere (centre, r^2 with a little to spare).
+static __global__ void pack_cull_kernel(const float4 *ga, const int4 *tiles, int n_tiles, float4 *gd) {
+    const int k = blockIdx.x;
+    if (k >= n_tiles) return;
+    const int4 td = tiles[k];
+    if (td.x != 2 && td.x != 0) return;
+    for (int j = threadIdx.x; 2 * j < td.z; j += blockDim.x) {
+        float4 a = ga[td.y + 2 * j];
+        // (an odd tile's last entry: a partner that is never near -- the scan tests that primitive on its own anyway)
+        float4 b = 2 * j + 1 < td.z ? ga[td.y + 2 * j + 1] : make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0xff800000));
+        if (td.x == 0) {
+            a.w = a.w * a.w * 1.0001f;
+            if (2 * j + 1 < td.z) b.w = b.w * b.w * 1.0001f;
+        }
+        gd[td.w + 2 * j] = make_float4(a.x, b.x, a.y, b.y);
+        gd[td.w + 2 * j + 1] = make_float4(a.z, b.z, -a.w, -b.w);
+    }
+}
+
 // ---- K2 (v0): one thread per pixel, loops exactly as shader.wgsl main() ----------------------------
 // Kept as the plain device restatement (and the instrumented build); the production kernel is
 // trace_persistent_kernel below.

@@ -157,7 +157,7 @@ struct SrcGrid : SrcGlobal {
 #endif
 struct SrcTiled : SrcGlobal {
     static constexpr bool kTiled = true;
-    static constexpr int kTileSlots = 2 * 3 * TRT_TILE;      // two buffers of (ga, gb, gc)[TRT_TILE]
+    static constexpr int kTileSlots = 2 * 4 * TRT_TILE;      // two buffers of (ga, gb, gc, gd)[TRT_TILE]
     static constexpr int kCtasPerSm = TRT_TILED_CTAS;        // 6: 80 registers; the scan loop must not spill
     __device__ SrcTiled(const SceneView &s, const LightView &l) : SrcGlobal(s, l) {}
 };
@@ -165,6 +165,7 @@ struct SrcTiled : SrcGlobal {
 struct TileAcc {
     const float4 *a, *b, *c;
     int base;
+    const float4 *d;     // triangle tiles: the pair-packed cull entries (SceneView::gd), tile-relative
     __device__ __forceinline__ float4 ga(int i) const { return a[i - base]; }
     __device__ __forceinline__ float4 gb(int i) const { return b[i - base]; }
     __device__ __forceinline__ float4 gc(int i) const { return c[i - base]; }
@@ -476,18 +477,81 @@ struct Tracer {
     // aligned plane; of a slab pair only the plane ahead of the origin is evaluated (the other one has
     // t <= 0 or a larger t), except when that plane is closer than t_min: then the second plane is
     // tested too, as hit_scene would.
+    // ---- the cull of scan_run's long triangle runs (TRT_V_TRI_CULL); returns the first index it has not handled ----
+    static __device__ __forceinline__ bool tri_far_away(const float4 v0r, float3 ro, float3 rd) {
+        const float3 tc = V::sub(xyz(v0r), ro);
+        const float t_ca = V::dot(tc, rd);
+        const float tcc = V::dot(tc, tc);
+        return V::nmadd(tcc, t_ca, t_ca) > __fmaf_rn(2e-5f, tcc, v0r.w);
+    }
+    template <class ACC, class FULL>
+    __device__ __forceinline__ int tri_cull(const ACC &acc, const int4 run, float3 ro, float3 rd, FULL &full) {
+        int i = run.y;
+        // four at a time: the four loads in flight together, four independent chains, then the branches
+        for (; i + 4 <= run.z; i += 4) {
+            const float4 w0 = acc.ga(i), w1 = acc.ga(i + 1), w2 = acc.ga(i + 2), w3 = acc.ga(i + 3);
+            const bool f0 = tri_far_away(w0, ro, rd), f1 = tri_far_away(w1, ro, rd), f2 = tri_far_away(w2, ro, rd), f3_ = tri_far_away(w3, ro, rd);
+            if (!f0) full(i);
+            if (!f1) full(i + 1);
+            if (!f2) full(i + 2);
+            if (!f3_) full(i + 3);
+        }
+        for (; i < run.z; i++)
+            if (!tri_far_away(acc.ga(i), ro, rd)) full(i);
+        return i;
+    }
+    // A staged tile: TWO triangles per step on packed FP32 pairs (f2_*: FADD2 / FMUL2 / FFMA2).  The same inequality,
+    // |tc|^2 - (tc . d)^2 > 2e-5 |tc|^2 + R, arranged as |tc|^2 * (1 - 2e-5) + (-R) > (tc . d)^2 so that it needs no negation:
+    // 11 packed instructions and two compares for two triangles (scalar: 12 + 1 each).
+    template <class FULL>
+    __device__ __forceinline__ int tri_cull(const TileAcc &acc, const int4 run, float3 ro, float3 rd, FULL &full) {
+        const f2_t nrx = f2_pack(-ro.x, -ro.x), nry = f2_pack(-ro.y, -ro.y), nrz = f2_pack(-ro.z, -ro.z);
+        const f2_t dx = f2_pack(rd.x, rd.x), dy = f2_pack(rd.y, rd.y), dz = f2_pack(rd.z, rd.z);
+        const f2_t k2 = f2_pack(1.0f - 2e-5f, 1.0f - 2e-5f);
+        const ulonglong2 *d = reinterpret_cast<const ulonglong2 *>(acc.d);
+        const int n_pairs = (run.z - run.y) >> 1;
+#pragma unroll 2
+        for (int p = 0; p < n_pairs; p++) {
+            const ulonglong2 q0 = d[2 * p], q1 = d[2 * p + 1];
+            const f2_t tcx = f2_add(q0.x, nrx), tcy = f2_add(q0.y, nry), tcz = f2_add(q1.x, nrz);
+            const f2_t tca = f2_fma(tcz, dz, f2_fma(tcy, dy, f2_mul(tcx, dx)));
+            const f2_t tcc = f2_fma(tcz, tcz, f2_fma(tcy, tcy, f2_mul(tcx, tcx)));
+            float l0, l1, r0, r1;
+            f2_unpack(f2_fma(tcc, k2, q1.y), l0, l1);
+            f2_unpack(f2_mul(tca, tca), r0, r1);
+            if (!(l0 > r0)) full(run.y + 2 * p);
+            if (!(l1 > r1)) full(run.y + 2 * p + 1);
+        }
+        int i = run.y + 2 * n_pairs;
+        if (run.x == 2)
+            for (; i < run.z; i++)
+                if (!tri_far_away(acc.ga(i), ro, rd)) full(i);
+        return i;
+    }
+    // spheres: only a staged tile has cull entries for them (an odd last sphere is left to the caller's loop)
+    template <class ACC, class FULL>
+    __device__ __forceinline__ int sph_cull(const ACC &, const int4 run, float3, float3, FULL &) { return run.y; }
+    template <class FULL>
+    __device__ __forceinline__ int sph_cull(const TileAcc &acc, const int4 run, float3 ro, float3 rd, FULL &full) { return tri_cull(acc, run, ro, rd, full); }
+
     // the tests of one run [begin, end) of primitives of one type, geometry through `acc` (global / constant /
     // staged tile); `closest` and `best` carry the scan state (shader.wgsl:255-292)
     template <int UNROLL, class ACC>
     __device__ __forceinline__ void scan_run(const ACC &acc, const int4 run, float3 ro, float3 rd, float3 inv, float t_min,
                                              float &closest, int &best) {
             if (run.x == 0) {
-#pragma unroll UNROLL
-                for (int i = run.y; i < run.z; i++) {
+                auto full = [&](int i) {
                     uint32_t cost;
                     const float t = test_sphere(ro, rd, acc.ga(i), acc.gb(i).x, t_min, closest, cost);
                     if (t > 0.0f) { closest = t; best = i; }
-                }
+                };
+                int i = run.y;
+#if TRT_V_TRI_CULL
+                // a staged tile: the packed-pair cull (centre and r^2 in gd) in front of the sphere test as well
+                if (run.z - run.y >= 8) i = sph_cull(acc, run, ro, rd, full);
+#endif
+#pragma unroll UNROLL
+                for (; i < run.z; i++) full(i);
             } else if (run.x >= 3 && run.x <= 8) {
                 const int axis = run.x >= 6 ? run.x - 6 : run.x - 3;
                 const float o_a = axis == 0 ? ro.x : axis == 1 ? ro.y : ro.z;
@@ -547,17 +611,7 @@ struct Tracer {
                 // r^2 in ga.w, written by repack_kernel with 10 % to spare) and 12 arithmetic instructions instead of
                 // three loads and ~25; d2 = |tc|^2 - (tc . d)^2 is as exact as |tc|^2 * 1e-6 (|d| = 1 to a few ulp,
                 // cancellation), hence the second term.  Survivors run the test as written: accepted hits are unchanged.
-                if (run.z - run.y >= 8) {
-#pragma unroll UNROLL
-                    for (; i < run.z; i++) {
-                        const float4 v0r = acc.ga(i);
-                        const float3 tc = V::sub(xyz(v0r), ro);
-                        const float t_ca = V::dot(tc, rd);
-                        const float tcc = V::dot(tc, tc);
-                        if (V::nmadd(tcc, t_ca, t_ca) > __fmaf_rn(2e-5f, tcc, v0r.w)) continue;
-                        full(i);
-                    }
-                }
+                if (run.z - run.y >= 8) i = tri_cull(acc, run, ro, rd, full);
 #endif
 #pragma unroll UNROLL
                 for (; i < run.z; i++) full(i);
@@ -635,7 +689,7 @@ struct Tracer {
 
 #ifndef __CUDACC_RTC__
     // CTA-cooperative form of scan_native (SrcTiled): every thread of the CTA must call it, the same number of
-    // times.  `tile` = 2 x 3 x TRT_TILE float4 of shared memory.  any_hit: the caller only reads t < 0
+    // times.  `tile` = 2 x 4 x TRT_TILE float4 of shared memory.  any_hit: the caller only reads t < 0
     // (shader.wgsl:400-402), so a warp whose lanes have all found an occluder (or have nothing to look for)
     // stops testing; it keeps taking part in the staging and the barriers.
     // `mbar`: two mbarriers in shared memory (initialised once by the kernel, count 1), `phase`: the parity each of them
@@ -652,19 +706,25 @@ struct Tracer {
         auto stage = [&](int k) {
             if (tid != 0) return;
             const int4 td = __ldg(&sc.tiles[k]);
-            float4 *buf = tile + (k & 1) * 3 * TRT_TILE;
+            float4 *buf = tile + (k & 1) * 4 * TRT_TILE;
             const unsigned bytes = (unsigned)td.z * 16u;
+            const unsigned dbytes = td.x == 2 || td.x == 0 ? (unsigned)((td.z + 1) & ~1) * 16u : 0u;      // cull entries of a triangle / sphere tile
             const unsigned bar = (unsigned)__cvta_generic_to_shared(&mbar[k & 1]);
             // the buffer was read with ordinary loads up to the barrier the caller has just passed: order them before
             // the asynchronous proxy's writes
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(3u * bytes) : "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(3u * bytes + dbytes) : "memory");
             const float4 *src[3] = {sc.ga + td.y, sc.gb + td.y, sc.gc + td.y};
 #pragma unroll
             for (int a = 0; a < 3; a++)
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                                  (unsigned)__cvta_generic_to_shared(buf + a * TRT_TILE)),
                              "l"(src[a]), "r"(bytes), "r"(bar)
+                             : "memory");
+            if (dbytes)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                 (unsigned)__cvta_generic_to_shared(buf + 3 * TRT_TILE)),
+                             "l"(sc.gd + td.w), "r"(dbytes), "r"(bar)
                              : "memory");
         };
         auto wait_tile = [&](int k) {
@@ -680,7 +740,9 @@ struct Tracer {
         (void)mbar; (void)phase;
         auto stage = [&](int k) {
             const int4 td = __ldg(&sc.tiles[k]);
-            float4 *buf = tile + (k & 1) * 3 * TRT_TILE;
+            float4 *buf = tile + (k & 1) * 4 * TRT_TILE;
+            if (td.x == 2 || td.x == 0)
+                for (int j = tid; j < ((td.z + 1) & ~1); j += (int)blockDim.x) __pipeline_memcpy_async(&buf[3 * TRT_TILE + j], &sc.gd[td.w + j], sizeof(float4));
             for (int j = tid; j < td.z; j += (int)blockDim.x) {
                 __pipeline_memcpy_async(&buf[j], &sc.ga[td.y + j], sizeof(float4));
                 __pipeline_memcpy_async(&buf[TRT_TILE + j], &sc.gb[td.y + j], sizeof(float4));
@@ -698,8 +760,8 @@ struct Tracer {
             if (k + 1 < n_tiles) stage(k + 1);
             if (!warp_done) {
                 const int4 td = __ldg(&sc.tiles[k]);
-                const float4 *buf = tile + (k & 1) * 3 * TRT_TILE;
-                TileAcc acc{buf, buf + TRT_TILE, buf + 2 * TRT_TILE, td.y};
+                const float4 *buf = tile + (k & 1) * 4 * TRT_TILE;
+                TileAcc acc{buf, buf + TRT_TILE, buf + 2 * TRT_TILE, td.y, buf + 3 * TRT_TILE};
                 scan_run<4>(acc, make_int4(td.x, td.y, td.y + td.z, 0), ro, rd, inv, t_min, closest, best);
                 if (any_hit) warp_done = __all_sync(0xffffffffu, best >= 0 || !(t_max > t_min));
             }
