@@ -160,14 +160,42 @@ __device__ __forceinline__ float rcp_native(float x) { float y; asm("rcp.approx.
 __device__ __forceinline__ float rsqrt_native(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float sqrt_native(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
+// TRT_V_PACKED: conv 2's element-wise float3 helpers put the x and y components through ONE packed instruction (FADD2 /
+// FMUL2 / FFMA2, a scalar operand is broadcast for free) and z through a scalar one: two issue slots instead of three.
+// Every lane's operation is the IEEE operation of the scalar form (the products and sums conv 2 contracts to FFMA are
+// written as fma here), so only values the compiler used to contract differently can move by an ulp.
+#ifndef TRT_V_PACKED
+#define TRT_V_PACKED 1
+#endif
+__device__ __forceinline__ f2_t f2z_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2z_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2z_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2z_fma(f2_t a, f2_t b, f2_t c) { f2_t r; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f2_t xy2(float3 a) { return f2_pack(a.x, a.y); }
+__device__ __forceinline__ f2_t ss2(float s) { return f2_pack(s, s); }
+__device__ __forceinline__ float3 f3z(f2_t xy, float z) { float x, y; f2_unpack(xy, x, y); return f3(x, y, z); }
+
 // ---- vector helpers (shader.wgsl:83-101,126-140,225-232) ----------------------------------------
 template <int CONV> struct M {
-    static __device__ __forceinline__ float3 add(float3 a, float3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
-    static __device__ __forceinline__ float3 sub(float3 a, float3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
-    static __device__ __forceinline__ float3 scale(float3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
-    static __device__ __forceinline__ float3 mulv(float3 a, float3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+    static constexpr bool kPacked = CONV == 2 && TRT_V_PACKED != 0;
+    static __device__ __forceinline__ float3 add(float3 a, float3 b) {
+        if (kPacked) return f3z(f2z_add(xy2(a), xy2(b)), a.z + b.z);
+        return f3(a.x + b.x, a.y + b.y, a.z + b.z);
+    }
+    static __device__ __forceinline__ float3 sub(float3 a, float3 b) {
+        if (kPacked) return f3z(f2z_sub(xy2(a), xy2(b)), a.z - b.z);
+        return f3(a.x - b.x, a.y - b.y, a.z - b.z);
+    }
+    static __device__ __forceinline__ float3 scale(float3 a, float s) {
+        if (kPacked) return f3z(f2z_mul(xy2(a), ss2(s)), a.z * s);
+        return f3(a.x * s, a.y * s, a.z * s);
+    }
+    static __device__ __forceinline__ float3 mulv(float3 a, float3 b) {
+        if (kPacked) return f3z(f2z_mul(xy2(a), xy2(b)), a.z * b.z);
+        return f3(a.x * b.x, a.y * b.y, a.z * b.z);
+    }
     static __device__ __forceinline__ float3 divs(float3 a, float s) {                              // == a.x/s, a.y/s, a.z/s
-        if (CONV == 2) { const float y = rcp_native(s); return f3(a.x * y, a.y * y, a.z * y); }
+        if (CONV == 2) { const float y = rcp_native(s); return scale(a, y); }
         return div3_rn(a, s);
     }
     static __device__ __forceinline__ float div(float a, float b) { return CONV == 2 ? a * rcp_native(b) : a / b; }
@@ -181,14 +209,18 @@ template <int CONV> struct M {
         return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
     }
     static __device__ __forceinline__ float3 axpy(float3 a, float3 b, float s) {          // a + b*s
+        if (kPacked) return f3z(f2z_fma(xy2(b), ss2(s), xy2(a)), __fmaf_rn(b.z, s, a.z));
         if (CONV) return f3(__fmaf_rn(b.x, s, a.x), __fmaf_rn(b.y, s, a.y), __fmaf_rn(b.z, s, a.z));
         return f3(a.x + b.x * s, a.y + b.y * s, a.z + b.z * s);
     }
     static __device__ __forceinline__ float3 vmad(float3 a, float3 b, float3 c) {         // a + b*c
+        if (kPacked) return f3z(f2z_fma(xy2(b), xy2(c), xy2(a)), __fmaf_rn(b.z, c.z, a.z));
         if (CONV) return f3(__fmaf_rn(b.x, c.x, a.x), __fmaf_rn(b.y, c.y, a.y), __fmaf_rn(b.z, c.z, a.z));
         return f3(a.x + b.x * c.x, a.y + b.y * c.y, a.z + b.z * c.z);
     }
     static __device__ __forceinline__ float3 lin3(float3 a, float s, float3 b, float t, float3 c, float u) {
+        if (kPacked)
+            return f3z(f2z_fma(xy2(c), ss2(u), f2z_fma(xy2(b), ss2(t), f2z_mul(xy2(a), ss2(s)))), __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
         if (CONV)
             return f3(__fmaf_rn(c.x, u, __fmaf_rn(b.x, t, a.x * s)), __fmaf_rn(c.y, u, __fmaf_rn(b.y, t, a.y * s)),
                       __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
@@ -196,11 +228,12 @@ template <int CONV> struct M {
     }
     static __device__ __forceinline__ float length(float3 v) { return sqrt(dot(v, v)); }
     static __device__ __forceinline__ float3 normalize(float3 v) {
-        if (CONV == 2) { const float y = rsqrt_native(dot(v, v)); return f3(v.x * y, v.y * y, v.z * y); }
+        if (CONV == 2) { const float y = rsqrt_native(dot(v, v)); return scale(v, y); }
         return divs(v, length(v));
     }
     static __device__ __forceinline__ float3 reflect(float3 v, float3 n) {                 // shader.wgsl:138-140
         float k = 2.0f * dot(v, n);
+        if (kPacked) return f3z(f2z_fma(xy2(n), ss2(-k), xy2(v)), __fmaf_rn(n.z, -k, v.z));
         if (CONV) return f3(__fmaf_rn(n.x, -k, v.x), __fmaf_rn(n.y, -k, v.y), __fmaf_rn(n.z, -k, v.z));
         return sub(v, scale(n, k));
     }
