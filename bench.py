@@ -13,7 +13,7 @@ fixed as N grows => "scaling": "strong").  --workload c1|c2|c4 select the other 
 `value`  : device-resident (scene + buffers in HBM; trace + accumulate + quantise of the own rows + row-length all-gather).
 `e2e`    : the same through trt_render_frame with HOST buffers: uniforms in, byte stream out (pinned).
 `roofline`: trace kernel, FP32: achieved = F_min (algorithmic flops) / CUDA-event time.
-`roofline_quantise`: the on-device quantiser (pack + scan + emit), algorithmic bytes / its CUDA-event time / HBM peak.
+`roofline_quantise`: the on-device quantiser (one pass: quant_fused_kernel), algorithmic bytes / its CUDA-event time / HBM peak.
 `cpu_baseline`: the reference's shader compiled for the host (oracle/_ref: shader.wgsl transliterated to C, kind
             "reference"; the hand-written port, kind "port", where _ref did not travel) on a bounded strided pixel
             sample of the same frame, all host threads.
@@ -39,7 +39,7 @@ sys.path.insert(0, ROOT)
 import __graft_entry__ as graft  # noqa: E402
 
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12      # 74.45: SMs x lanes x 2 x max clock
-QUANT_KERNELS = "quant_pack_kernel + quant_scan_kernel + quant_emit_kernel + quant_row_len_kernel"
+QUANT_KERNELS = "quant_fused_kernel (one pass, decoupled look-back) + quant_row_len_from_starts_kernel + the memset of the tile states"
 
 
 def workload(name, O, args):
