@@ -154,6 +154,7 @@ typedef unsigned long long f2_t;
 __device__ __forceinline__ f2_t f2_pack(float lo, float hi) { f2_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 __device__ __forceinline__ void f2_unpack(f2_t v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
 __device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f2_t f2_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) { f2_t r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
 __device__ __forceinline__ float rcp_native(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -167,31 +168,48 @@ __device__ __forceinline__ float sqrt_native(float x) { float y; asm("sqrt.appro
 #ifndef TRT_V_PACKED
 #define TRT_V_PACKED 1
 #endif
+// The strict conventions pack ADDITIONS AND SUBTRACTIONS only (and, in conv 1, the helpers that are one fused multiply-add
+// by definition).  ptxas 12.9 contracts `mul.rn.f32x2` followed by `add.rn.f32x2` into FFMA2 whatever --fmad says, and
+// even sees through fma(a, b, -0.0) used as an exact product (tools/micro: z.cu, z2.cu) -- a packed product feeding a
+// sum would silently lose a rounding.  A packed lane of an addition is bit for bit the scalar IEEE addition.
+// Measured (profiles/r2_ab_packed_fp32.txt): bit-exact (the strict suite passes), pool machine 81.6 -> 79.9 ms, one pixel per
+// lane 85.1 -> 85.6 ms on the A/B frame: not worth depending on what ptxas leaves alone -- off.
+#ifndef TRT_V_PACKED_STRICT
+#define TRT_V_PACKED_STRICT 0
+#endif
 __device__ __forceinline__ f2_t f2z_add(f2_t a, f2_t b) { f2_t r; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ f2_t f2z_sub(f2_t a, f2_t b) { f2_t r; asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ f2_t f2z_mul(f2_t a, f2_t b) { f2_t r; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ f2_t f2z_fma(f2_t a, f2_t b, f2_t c) { f2_t r; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+// by convention: conv 2 flushes denormals like the rest of its translation unit (-use_fast_math); the strict conventions
+// use the plain IEEE forms, so a packed lane is bit for bit the scalar operation it replaces
+template <int CONV> __device__ __forceinline__ f2_t p_add(f2_t a, f2_t b) { return CONV == 2 ? f2z_add(a, b) : f2_add(a, b); }
+template <int CONV> __device__ __forceinline__ f2_t p_sub(f2_t a, f2_t b) { return CONV == 2 ? f2z_sub(a, b) : f2_sub(a, b); }
+template <int CONV> __device__ __forceinline__ f2_t p_mul(f2_t a, f2_t b) { return CONV == 2 ? f2z_mul(a, b) : f2_mul(a, b); }
+template <int CONV> __device__ __forceinline__ f2_t p_fma(f2_t a, f2_t b, f2_t c) { return CONV == 2 ? f2z_fma(a, b, c) : f2_fma(a, b, c); }
 __device__ __forceinline__ f2_t xy2(float3 a) { return f2_pack(a.x, a.y); }
 __device__ __forceinline__ f2_t ss2(float s) { return f2_pack(s, s); }
 __device__ __forceinline__ float3 f3z(f2_t xy, float z) { float x, y; f2_unpack(xy, x, y); return f3(x, y, z); }
 
 // ---- vector helpers (shader.wgsl:83-101,126-140,225-232) ----------------------------------------
 template <int CONV> struct M {
-    static constexpr bool kPacked = CONV == 2 && TRT_V_PACKED != 0;
+    static constexpr bool kPacked = CONV == 2 && TRT_V_PACKED != 0;                 // products, sums and fused forms
+    static constexpr bool kPackedAdd = kPacked || (CONV != 2 && TRT_V_PACKED_STRICT != 0);   // sums only
+    static constexpr bool kPackedFma = kPacked || (CONV == 1 && TRT_V_PACKED_STRICT != 0);   // helpers that ARE one fma
     static __device__ __forceinline__ float3 add(float3 a, float3 b) {
-        if (kPacked) return f3z(f2z_add(xy2(a), xy2(b)), a.z + b.z);
+        if (kPackedAdd) return f3z(p_add<CONV>(xy2(a), xy2(b)), a.z + b.z);
         return f3(a.x + b.x, a.y + b.y, a.z + b.z);
     }
     static __device__ __forceinline__ float3 sub(float3 a, float3 b) {
-        if (kPacked) return f3z(f2z_sub(xy2(a), xy2(b)), a.z - b.z);
+        if (kPackedAdd) return f3z(p_sub<CONV>(xy2(a), xy2(b)), a.z - b.z);
         return f3(a.x - b.x, a.y - b.y, a.z - b.z);
     }
     static __device__ __forceinline__ float3 scale(float3 a, float s) {
-        if (kPacked) return f3z(f2z_mul(xy2(a), ss2(s)), a.z * s);
+        if (kPacked) return f3z(p_mul<CONV>(xy2(a), ss2(s)), a.z * s);
         return f3(a.x * s, a.y * s, a.z * s);
     }
     static __device__ __forceinline__ float3 mulv(float3 a, float3 b) {
-        if (kPacked) return f3z(f2z_mul(xy2(a), xy2(b)), a.z * b.z);
+        if (kPacked) return f3z(p_mul<CONV>(xy2(a), xy2(b)), a.z * b.z);
         return f3(a.x * b.x, a.y * b.y, a.z * b.z);
     }
     static __device__ __forceinline__ float3 divs(float3 a, float s) {                              // == a.x/s, a.y/s, a.z/s
@@ -209,18 +227,18 @@ template <int CONV> struct M {
         return f3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
     }
     static __device__ __forceinline__ float3 axpy(float3 a, float3 b, float s) {          // a + b*s
-        if (kPacked) return f3z(f2z_fma(xy2(b), ss2(s), xy2(a)), __fmaf_rn(b.z, s, a.z));
+        if (kPackedFma) return f3z(p_fma<CONV>(xy2(b), ss2(s), xy2(a)), __fmaf_rn(b.z, s, a.z));
         if (CONV) return f3(__fmaf_rn(b.x, s, a.x), __fmaf_rn(b.y, s, a.y), __fmaf_rn(b.z, s, a.z));
         return f3(a.x + b.x * s, a.y + b.y * s, a.z + b.z * s);
     }
     static __device__ __forceinline__ float3 vmad(float3 a, float3 b, float3 c) {         // a + b*c
-        if (kPacked) return f3z(f2z_fma(xy2(b), xy2(c), xy2(a)), __fmaf_rn(b.z, c.z, a.z));
+        if (kPackedFma) return f3z(p_fma<CONV>(xy2(b), xy2(c), xy2(a)), __fmaf_rn(b.z, c.z, a.z));
         if (CONV) return f3(__fmaf_rn(b.x, c.x, a.x), __fmaf_rn(b.y, c.y, a.y), __fmaf_rn(b.z, c.z, a.z));
         return f3(a.x + b.x * c.x, a.y + b.y * c.y, a.z + b.z * c.z);
     }
     static __device__ __forceinline__ float3 lin3(float3 a, float s, float3 b, float t, float3 c, float u) {
         if (kPacked)
-            return f3z(f2z_fma(xy2(c), ss2(u), f2z_fma(xy2(b), ss2(t), f2z_mul(xy2(a), ss2(s)))), __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
+            return f3z(p_fma<CONV>(xy2(c), ss2(u), p_fma<CONV>(xy2(b), ss2(t), p_mul<CONV>(xy2(a), ss2(s)))), __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
         if (CONV)
             return f3(__fmaf_rn(c.x, u, __fmaf_rn(b.x, t, a.x * s)), __fmaf_rn(c.y, u, __fmaf_rn(b.y, t, a.y * s)),
                       __fmaf_rn(c.z, u, __fmaf_rn(b.z, t, a.z * s)));
@@ -233,7 +251,7 @@ template <int CONV> struct M {
     }
     static __device__ __forceinline__ float3 reflect(float3 v, float3 n) {                 // shader.wgsl:138-140
         float k = 2.0f * dot(v, n);
-        if (kPacked) return f3z(f2z_fma(xy2(n), ss2(-k), xy2(v)), __fmaf_rn(n.z, -k, v.z));
+        if (kPackedFma) return f3z(p_fma<CONV>(xy2(n), ss2(-k), xy2(v)), __fmaf_rn(n.z, -k, v.z));
         if (CONV) return f3(__fmaf_rn(n.x, -k, v.x), __fmaf_rn(n.y, -k, v.y), __fmaf_rn(n.z, -k, v.z));
         return sub(v, scale(n, k));
     }
