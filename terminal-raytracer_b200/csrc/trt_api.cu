@@ -368,6 +368,12 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
                 sm.sph[j] = make_float4(p.sphere_center.x, p.sphere_center.y, p.sphere_center.z, p.sphere_radius);
                 sm.sph_r2[j] = make_float4(p.sphere_radius * p.sphere_radius, 0.0f, 0.0f, 0.0f);
             }
+            for (uint32_t k = 0; 2 * k + 1 < ns; k++) {
+                const trt_primitive &a = prims[2 * k], &b = prims[2 * k + 1];
+                sm.sph_pair[3 * k] = make_float4(a.sphere_center.x, b.sphere_center.x, a.sphere_center.y, b.sphere_center.y);
+                sm.sph_pair[3 * k + 1] = make_float4(a.sphere_center.z, b.sphere_center.z, a.sphere_radius, b.sphere_radius);
+                sm.sph_pair[3 * k + 2] = make_float4(a.sphere_radius * a.sphere_radius, b.sphere_radius * b.sphere_radius, 0.0f, 0.0f);
+            }
             for (uint32_t j = 0; j < np; j++) {
                 const trt_primitive &p = prims[ns + j];
                 const uint8_t ty = types[ns + j];
@@ -375,6 +381,13 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
                 sm.pl_p[j] = make_float4(p.plane_point.x, p.plane_point.y, p.plane_point.z, 0.0f);
                 memcpy(&sm.pl_p[j].w, &kind, 4);
                 sm.pl_n[j] = make_float4(p.plane_normal.x, p.plane_normal.y, p.plane_normal.z, 0.0f);
+            }
+            for (uint32_t k = 0; 2 * k + 1 < np; k++) {          // two walls on one axis: their coordinates side by side
+                int ka, kb;
+                memcpy(&ka, &sm.pl_p[2 * k].w, 4); memcpy(&kb, &sm.pl_p[2 * k + 1].w, 4);
+                const float4 a = sm.pl_p[2 * k], b = sm.pl_p[2 * k + 1];
+                sm.pl_pair[k] = ka == kb && ka < 3 ? make_float2(ka == 0 ? a.x : ka == 1 ? a.y : a.z, ka == 0 ? b.x : ka == 1 ? b.y : b.z)
+                                                   : make_float2(0.0f, 0.0f);
             }
             for (uint32_t j = 0; j < nt; j++) {
                 const trt_primitive &p = prims[ns + np + j];

@@ -49,8 +49,14 @@ struct SmallScene {
     unsigned tri_zero, pad0_, pad1_, pad2_;               // ShapeFixed::TZ of this scene   // light list: count, bit k set = light k is a sphere
     float4 sph[TRT_SMALL_S];          // (c, r)
     float4 sph_r2[TRT_SMALL_S];       // (r*r, -, -, -)
+    // spheres 2k and 2k + 1 side by side for the packed pre-reject of scan_small_native (TRT_V_PACKED):
+    // [3k] = (x_a, x_b, y_a, y_b), [3k + 1] = (z_a, z_b, r_a, r_b), [3k + 2] = (r_a^2, r_b^2, -, -)
+    float4 sph_pair[3 * (TRT_SMALL_S / 2)];
     float4 pl_p[TRT_SMALL_P];         // (point, kind as int bits): kind 0 / 1 / 2 = normal is +-unit x / y / z, 3 = general
     float4 pl_n[TRT_SMALL_P];         // raw normal (general planes)
+    // planes 2k and 2k + 1 when both are axis-aligned on the SAME axis (the walls of a box): their coordinates on that
+    // axis side by side, for one packed multiply-add (scan_small_native with a compile-time shape, TRT_V_PACKED)
+    float2 pl_pair[TRT_SMALL_P / 2];
     float4 tri_v0[TRT_SMALL_T], tri_e1[TRT_SMALL_T], tri_e2[TRT_SMALL_T];
 };
 TRT_CONSTANT(SmallScene c_small);
@@ -275,6 +281,20 @@ struct Tracer {
         float root = t_ca - sq;
         if (root <= t_min || closest <= root) {
             cost = 38;
+            root = t_ca + sq;
+            if (root <= t_min || closest <= root) return -1.0f;
+        }
+        return root;
+    }
+    // test_sphere from its pre-reject on, given t_ca = tc . d, |tc|^2 and dist2 (the packed pair path of scan_small_native)
+    __device__ __forceinline__ float sphere_tail(float t_ca, float tcc, float dist2, float r, float r2, float t_min, float closest) const {
+        if (dist2 > r2 || t_ca + r < t_min || t_ca - r > closest) return -1.0f;
+        const float c = tcc - r2;
+        const float disc = V::msub(t_ca, t_ca, c);
+        if (disc < 0.0f) return -1.0f;
+        const float sq = sqrtf(disc);
+        float root = t_ca - sq;
+        if (root <= t_min || closest <= root) {
             root = t_ca + sq;
             if (root <= t_min || closest <= root) return -1.0f;
         }
@@ -783,6 +803,33 @@ struct Tracer {
         const int n_sph = SHAPE::kFixed ? SHAPE::NS : c_small.n_sph;
         const int n_pl = SHAPE::kFixed ? SHAPE::NP : c_small.n_pl;
         const int n_tri = SHAPE::kFixed ? SHAPE::NT : c_small.n_tri;
+#if TRT_V_PACKED
+        // hit_sphere's distance pre-reject for TWO spheres at a time on packed pairs (sphere a in the low lane): tc = c - o,
+        // t_ca = tc . d, |tc|^2 and dist2 = |tc|^2 - t_ca^2 are 10 packed instructions for the pair instead of 10 each; the
+        // rest of the test (sphere_tail) is per sphere and sees the narrowed bound of its predecessor, as written.
+        const f2_t nox = ss2(-ro.x), noy = ss2(-ro.y), noz = ss2(-ro.z), pdx = ss2(rd.x), pdy = ss2(rd.y), pdz = ss2(rd.z);
+#pragma unroll
+        for (int k = 0; 2 * k < (SHAPE::kFixed ? SHAPE::NS : TRT_STATIC_S); k++) {
+            const int j = 2 * k;
+            if (j + 1 < (SHAPE::kFixed ? SHAPE::NS : TRT_STATIC_S) && j + 1 < n_sph) {
+                const float4 q0 = c_small.sph_pair[3 * k], q1 = c_small.sph_pair[3 * k + 1], q2 = c_small.sph_pair[3 * k + 2];
+                const f2_t tcx = f2z_add(f2_pack(q0.x, q0.y), nox), tcy = f2z_add(f2_pack(q0.z, q0.w), noy), tcz = f2z_add(f2_pack(q1.x, q1.y), noz);
+                const f2_t tca = f2z_fma(tcz, pdz, f2z_fma(tcy, pdy, f2z_mul(tcx, pdx)));
+                const f2_t tcc = f2z_fma(tcz, tcz, f2z_fma(tcy, tcy, f2z_mul(tcx, tcx)));
+                const f2_t d2 = f2z_sub(tcc, f2z_mul(tca, tca));          // (contracted to one FFMA2 with a negated product)
+                float ta, tb, ca, cb_, da, db;
+                f2_unpack(tca, ta, tb); f2_unpack(tcc, ca, cb_); f2_unpack(d2, da, db);
+                float t = sphere_tail(ta, ca, da, q1.z, q2.x, t_min, closest);
+                if (t > 0.0f) { closest = t; best = j; }
+                t = sphere_tail(tb, cb_, db, q1.w, q2.y, t_min, closest);
+                if (t > 0.0f) { closest = t; best = j + 1; }
+            } else if (j < n_sph) {
+                uint32_t cost;
+                const float t = test_sphere(ro, rd, c_small.sph[j], c_small.sph_r2[j].x, t_min, closest, cost);
+                if (t > 0.0f) { closest = t; best = j; }
+            }
+        }
+#else
 #pragma unroll
         for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NS : TRT_STATIC_S); j++) {
             if (j < n_sph) {
@@ -791,6 +838,7 @@ struct Tracer {
                 if (t > 0.0f) { closest = t; best = j; }
             }
         }
+#endif
 #if TRT_V_KEY
         // index field: 4 / 5 / 6 bits by the scene's primitive count (the same rule for a compile-time and a run-time
         // count, so that a specialised kernel and the run-time-count kernel quantise t alike); all ones = nothing found.
@@ -817,6 +865,7 @@ struct Tracer {
             const float3 inv = f3(fabsf(rd.x) >= 0.0001f ? rcp_native(rd.x) : nan, fabsf(rd.y) >= 0.0001f ? rcp_native(rd.y) : nan,
                                   fabsf(rd.z) >= 0.0001f ? rcp_native(rd.z) : nan);
             float3 roi = V::mulv(ro, inv);
+            float t_pair_hi = 0.0f;
 #if TRT_V_SHIFT_T || TRT_V_KEY
             roi = f3(roi.x + t_min, roi.y + t_min, roi.z + t_min);         // axis-aligned planes yield t' directly
 #endif
@@ -826,6 +875,16 @@ struct Tracer {
                     const float4 p = c_small.pl_p[j];
                     const int kind = SHAPE::kFixed ? SHAPE::kind(j) : __float_as_int(p.w);
                     float t;
+#if TRT_V_PACKED && (TRT_V_SHIFT_T || TRT_V_KEY)
+                    // two walls on one axis (compile-time shape): both t' in one FFMA2, the second one is kept for the next round
+                    if (SHAPE::kFixed && kind < 3 && (j & 1) && SHAPE::kind(j - 1) == kind) {
+                        t = t_pair_hi;
+                    } else if (SHAPE::kFixed && kind < 3 && !(j & 1) && j + 1 < SHAPE::NP && SHAPE::kind(j + 1) == kind) {
+                        const float2 pp = c_small.pl_pair[j >> 1];
+                        const float i_a = kind == 0 ? inv.x : kind == 1 ? inv.y : inv.z, r_a = kind == 0 ? roi.x : kind == 1 ? roi.y : roi.z;
+                        f2_unpack(f2z_fma(f2_pack(pp.x, pp.y), ss2(i_a), ss2(-r_a)), t, t_pair_hi);
+                    } else
+#endif
                     if (kind == 0) t = __fmaf_rn(p.x, inv.x, -roi.x);          // (p - o) / d as p * (1/d) - o * (1/d)
                     else if (kind == 1) t = __fmaf_rn(p.y, inv.y, -roi.y);
                     else if (kind == 2) t = __fmaf_rn(p.z, inv.z, -roi.z);
