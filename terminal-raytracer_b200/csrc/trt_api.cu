@@ -402,6 +402,24 @@ extern "C" int trt_upload_scene(trt_ctx *ctx, const trt_primitive *prims, uint32
                 if (e[b] == 0.0f) sm.tri_zero |= 1u << (6 * j + b);
         }
         sm.n_lights = (int)light_prim.size();
+        // triangle lights 2k and 2k + 1 side by side for the packed reach test of the bounce (trt_native.cuh): unit normal,
+        // plane offset dot(n, v0) and its magnitude, with the operation sequence of repack_kernel<0>
+        for (size_t k = 0; 2 * k + 1 < light_prim.size() && k < TRT_SMALL_LPAIRS; k++) {
+            float nx[2] = {0, 0}, ny[2] = {0, 0}, nz[2] = {0, 0}, off[2] = {0, 0};
+            for (int h = 0; h < 2; h++) {
+                const trt_primitive &p = prims[light_prim[2 * k + h]];
+                if (p.primitive_type != 2u) continue;
+                const float e1[3] = {p.triangle_v1.x - p.triangle_v0.x, p.triangle_v1.y - p.triangle_v0.y, p.triangle_v1.z - p.triangle_v0.z};
+                const float e2[3] = {p.triangle_v2.x - p.triangle_v0.x, p.triangle_v2.y - p.triangle_v0.y, p.triangle_v2.z - p.triangle_v0.z};
+                const float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+                const float len = sqrtf(cx * cx + cy * cy + cz * cz);
+                nx[h] = cx / len; ny[h] = cy / len; nz[h] = cz / len;
+                off[h] = nx[h] * p.triangle_v0.x + ny[h] * p.triangle_v0.y + nz[h] * p.triangle_v0.z;
+            }
+            sm.lt_pair[3 * k] = make_float4(nx[0], nx[1], ny[0], ny[1]);
+            sm.lt_pair[3 * k + 1] = make_float4(nz[0], nz[1], off[0], off[1]);
+            sm.lt_pair[3 * k + 2] = make_float4(fabsf(off[0]), fabsf(off[1]), 0.0f, 0.0f);
+        }
         for (size_t k = 0; k < light_prim.size() && k < 32; k++)
             if (prims[light_prim[k]].primitive_type == 0u) { sm.light_spheres |= 1 << k; sm.n_light_spheres++; }
         ctx->small = sm;

@@ -40,6 +40,7 @@ TRT_CONSTANT(ConstScene c_scene);      // one mirror per translation unit (stric
 #define TRT_SMALL_S 24         // capacity of the mirror: what a run-time specialised kernel (trt_jit.cuh) can take
 #define TRT_SMALL_P 8
 #define TRT_SMALL_T 8
+#define TRT_SMALL_LPAIRS 8      // pairs of lights mirrored for the packed reach test (= TRT_NV_MAX_LIGHTS / 2)
 #define TRT_STATIC_S 4         // slots the statically compiled run-time-count scan unrolls (ok: the scene fits these)
 #define TRT_STATIC_P 8
 #define TRT_STATIC_T 4
@@ -57,6 +58,9 @@ struct SmallScene {
     // planes 2k and 2k + 1 when both are axis-aligned on the SAME axis (the walls of a box): their coordinates on that
     // axis side by side, for one packed multiply-add (scan_small_native with a compile-time shape, TRT_V_PACKED)
     float2 pl_pair[TRT_SMALL_P / 2];
+    // triangle lights 2k and 2k + 1 side by side (the reach test of the bounce, trt_native.cuh): [3k] = (nx_a, nx_b, ny_a,
+    // ny_b), [3k + 1] = (nz_a, nz_b, off_a, off_b), [3k + 2] = (|off_a|, |off_b|, -, -); off = dot(n, v0)
+    float4 lt_pair[3 * TRT_SMALL_LPAIRS];
     float4 tri_v0[TRT_SMALL_T], tri_e1[TRT_SMALL_T], tri_e2[TRT_SMALL_T];
 };
 TRT_CONSTANT(SmallScene c_small);
@@ -126,6 +130,7 @@ struct ShapeAny {
     typedef RunsAny Runs;
     static constexpr bool kFixed = false, kFixedLights = false;
     static constexpr int NS = 0, NP = 0, NT = 0, NL = -1;
+    static constexpr unsigned KINDS = 0u, LSPH = 0u;
     static __host__ __device__ __forceinline__ constexpr int kind(int) { return 3; }
     static __host__ __device__ __forceinline__ constexpr bool light_is_sphere(int, int type) { return type == 0; }
     static __host__ __device__ __forceinline__ constexpr unsigned tri_zero(int) { return 0u; }
@@ -287,8 +292,9 @@ struct Tracer {
         return root;
     }
     // test_sphere from its pre-reject on, given t_ca = tc . d, |tc|^2 and dist2 (the packed pair path of scan_small_native)
-    __device__ __forceinline__ float sphere_tail(float t_ca, float tcc, float dist2, float r, float r2, float t_min, float closest) const {
-        if (dist2 > r2 || t_ca + r < t_min || t_ca - r > closest) return -1.0f;
+    // (far = t_ca + r, near = t_ca - r)
+    __device__ __forceinline__ float sphere_tail(float t_ca, float tcc, float dist2, float far, float near, float r2, float t_min, float closest) const {
+        if (dist2 > r2 || far < t_min || near > closest) return -1.0f;
         const float c = tcc - r2;
         const float disc = V::msub(t_ca, t_ca, c);
         if (disc < 0.0f) return -1.0f;
@@ -817,11 +823,13 @@ struct Tracer {
                 const f2_t tca = f2z_fma(tcz, pdz, f2z_fma(tcy, pdy, f2z_mul(tcx, pdx)));
                 const f2_t tcc = f2z_fma(tcz, tcz, f2z_fma(tcy, tcy, f2z_mul(tcx, tcx)));
                 const f2_t d2 = f2z_sub(tcc, f2z_mul(tca, tca));          // (contracted to one FFMA2 with a negated product)
-                float ta, tb, ca, cb_, da, db;
+                const f2_t rr = f2_pack(q1.z, q1.w);
+                float ta, tb, ca, cb_, da, db, fa, fb, na, nb;
                 f2_unpack(tca, ta, tb); f2_unpack(tcc, ca, cb_); f2_unpack(d2, da, db);
-                float t = sphere_tail(ta, ca, da, q1.z, q2.x, t_min, closest);
+                f2_unpack(f2z_add(tca, rr), fa, fb); f2_unpack(f2z_sub(tca, rr), na, nb);      // t_ca + r, t_ca - r
+                float t = sphere_tail(ta, ca, da, fa, na, q2.x, t_min, closest);
                 if (t > 0.0f) { closest = t; best = j; }
-                t = sphere_tail(tb, cb_, db, q1.w, q2.y, t_min, closest);
+                t = sphere_tail(tb, cb_, db, fb, nb, q2.y, t_min, closest);
                 if (t > 0.0f) { closest = t; best = j + 1; }
             } else if (j < n_sph) {
                 uint32_t cost;
@@ -867,7 +875,7 @@ struct Tracer {
             float3 roi = V::mulv(ro, inv);
             float t_pair_hi = 0.0f;
 #if TRT_V_SHIFT_T || TRT_V_KEY
-            roi = f3(roi.x + t_min, roi.y + t_min, roi.z + t_min);         // axis-aligned planes yield t' directly
+            roi = V::add(roi, f3(t_min, t_min, t_min));                    // axis-aligned planes yield t' directly
 #endif
 #pragma unroll
             for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NP : TRT_STATIC_P); j++) {
