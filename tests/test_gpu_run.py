@@ -113,8 +113,14 @@ def test_cli_on_a_pseudo_terminal(pkg):
 
     err = b""
     try:
-        pump(2.0)
-        n_before = b"".join(chunks).count(b"Frame: ")
+        # the first frame waits for the CUDA context, the module load and the run-time compile of the scene's kernel: seconds
+        # on a fresh box, so poll for it instead of assuming a start-up time
+        n_before = 0
+        for _ in range(120):
+            pump(0.5)
+            n_before = b"".join(chunks).count(b"Frame: ")
+            if n_before >= 1 or p.poll() is not None:
+                break
         assert n_before >= 1, b"".join(chunks)[:200]
         os.write(master, b"w")                     # move: the accumulation restarts at frame 1
         pump(0.5)
