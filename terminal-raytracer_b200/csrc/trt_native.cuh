@@ -60,6 +60,15 @@ namespace trt {
 #ifndef TRT_V_ORDERED_LATE
 #define TRT_V_ORDERED_LATE 1
 #endif
+// TRT_V_DUAL_SHADOW: a queue pass of the small-scene kernel takes the samples of TWO lights and sends both shadow rays
+// through one any-hit scan on packed pairs (Tracer::shadow2_small).  Measured (profiles/r2_ab_packed_fp32.txt): the queue
+// passes halve (16.7 M -> 8.3 M on the A/B frame) and a pass for two lights costs ~640 instead of ~1 030 instructions,
+// but at 64 registers the second ray's state spills into the bounce path (scatter 77 -> 107 instructions, post 26 -> 40):
+// 37.13 G instead of 37.05 G warp-instructions, 36.47 -> 39.78 ms.  With 72 registers (7 CTAs) 36.61 -> 36.39 ms
+// against 36.50 ms for the default: not adopted, 0 = one light per pass through the closest-hit scan.
+#ifndef TRT_V_DUAL_SHADOW
+#define TRT_V_DUAL_SHADOW 0
+#endif
 #define TRT_NV_RING 64           // queued hits per warp: at most 31 left over + 32 new ones per iteration
 #define TRT_NV_MAX_LIGHTS 16     // light mask bits in the entry's meta word
 
@@ -438,6 +447,10 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
         float qt = 1e10f;
         unsigned qowner = 0, qrest = 0, qslot = 0;
         uint32_t qrng = 0, qn = 0;
+        // TRT_V_DUAL_SHADOW (small scenes, conv 2): the samples of TWO lights per queue pass, both shadow rays in one scan
+        bool dual = false, qneedB = false;
+        float3 qdB = f3(0, 0, 1), qcB = f3(0, 0, 0);
+        float qtB = -1.0f;
         const uint32_t qe = (head + lane) & (TRT_NV_RING - 1u);
         if (SRC::kTiled) {
             // Large scenes: a scan costs ~0.5 M instructions per warp, so only NEEDED shadow rays may occupy a scan
@@ -557,11 +570,39 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                     qneed = nee_sample<CONV, SHAPE>(tr, k, P, N, C, A, __uint2float_rn(s1) * 2.3283064365386963e-10f,
                                        __uint2float_rn(qrng) * 2.3283064365386963e-10f, qo, qd, qt, qc);
                 }
+#if TRT_V_DUAL_SHADOW && TRT_V_PACKED && TRT_V_SHIFT_T && !TRT_V_KEY
+                if (!kStrict && small && qrest != 0u) {           // the next light some queued hit can see, in the same pass
+                    dual = true;
+                    const int k2 = k + __ffs((int)qrest);
+                    for (int i = k + 1; i < k2; i++) qrng = pcg_hash(pcg_hash(qrng));      // lights in between: only their draws
+                    const uint32_t s1b = pcg_hash(qrng);
+                    qrng = pcg_hash(s1b);
+                    if ((lmask >> k2) & 1u) {
+                        const float3 P = f3(ring[DQ_PX][qe], ring[DQ_PY][qe], ring[DQ_PZ][qe]);
+                        const float3 N = f3(ring[DQ_NX][qe], ring[DQ_NY][qe], ring[DQ_NZ][qe]);
+                        const float3 C = f3(ring[DQ_CX][qe], ring[DQ_CY][qe], ring[DQ_CZ][qe]);
+                        float3 qoB;
+                        qneedB = nee_sample<CONV, SHAPE>(tr, k2, P, N, C, C, __uint2float_rn(s1b) * 2.3283064365386963e-10f,
+                                            __uint2float_rn(qrng) * 2.3283064365386963e-10f, qoB, qdB, qtB, qcB);
+                        if (qneedB) qo = qoB;                     // (the same point, P + 0.001 N: set when only the second sample is needed)
+                    }
+                    sp_k = k2;
+                    qrest = uni >> (k2 + 1);
+                }
+#endif
             }
         }
         int best = -1;
         float t_hit = -1.0f;
+        bool occB = true;
         if (fp.max_depth != 0u) {
+#if TRT_V_DUAL_SHADOW && TRT_V_PACKED && TRT_V_SHIFT_T && !TRT_V_KEY
+            if (dual) {
+                bool occA;
+                tr.template shadow2_small<SHAPE>(qo, qd, qt, qdB, qtB, occA, occB);
+                t_hit = occA ? 1.0f : -1.0f;
+            } else
+#endif
             if (small) t_hit = tr.template scan_small_native<SHAPE>(qo, qd, qt, best);
 #ifndef __CUDACC_RTC__
             else if (SRC::kTiled) t_hit = tr.scan_native_tiled(qo, qd, mode == NM_ACTIVE || spass ? qt : -1.0f, best, s_tile, spass, s_mbar, tile_phase);
@@ -591,6 +632,7 @@ __device__ __forceinline__ void trace_native_body(const SceneView &sc, const Lig
                 // the entry's lights are summed in light order in a register, the entry's sum joins the owner's late
                 // sum once, at its last light, in posting order
                 if (lit) qsum = V::add(qsum, qc);
+                if (dual && qvalid && qneedB && !occB) qsum = V::add(qsum, qcB);
                 if (qrest) {
                     if (qvalid) ring[DQ_RNG][qe] = __uint_as_float(qrng);
                 } else {

@@ -960,6 +960,107 @@ struct Tracer {
         return best >= 0 ? closest : -1.0f;
     }
 
+#if TRT_V_PACKED && TRT_V_SHIFT_T && !TRT_V_KEY
+    // TWO shadow rays from one origin (the samples of two lights for one queued hit) through the canonical small scene
+    // in ONE pass, any-hit: the caller reads only `hit.t < 0` (shader.wgsl:400-402), and some primitive is accepted by
+    // hit_scene's narrowing scan iff some primitive has t in [t_min, t_max) -- the first one it accepts is tested
+    // against t_max itself -- so no bound is narrowed and no index kept.  Every t is computed as scan_small_native
+    // computes it (same operations, same order); the rays share the origin, so of a sphere test only tc . d and
+    // dist2 are per ray -- on packed pairs, ray A in the low lane -- and a wall's t' for both rays is one FFMA2.
+    // t_max <= t_min (a sample that is not needed: t_max = -1) accepts nothing.
+    template <class SHAPE>
+    __device__ __forceinline__ void shadow2_small(float3 o, float3 dA, float tA, float3 dB, float tB, bool &occA, bool &occB) {
+        const float t_min = 0.001f;
+        const int n_sph = SHAPE::kFixed ? SHAPE::NS : c_small.n_sph;
+        const int n_pl = SHAPE::kFixed ? SHAPE::NP : c_small.n_pl;
+        const int n_tri = SHAPE::kFixed ? SHAPE::NT : c_small.n_tri;
+        bool hA = false, hB = false;
+        const f2_t DX = f2_pack(dA.x, dB.x), DY = f2_pack(dA.y, dB.y), DZ = f2_pack(dA.z, dB.z);
+#pragma unroll
+        for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NS : TRT_STATIC_S); j++) {
+            if (j < n_sph) {
+                const float4 sp = c_small.sph[j];
+                const float r2 = c_small.sph_r2[j].x;
+                const float3 tc = V::sub(xyz(sp), o);
+                const float tcc = V::dot(tc, tc);
+                const f2_t tca = f2z_fma(ss2(tc.z), DZ, f2z_fma(ss2(tc.y), DY, f2z_mul(ss2(tc.x), DX)));
+                const f2_t d2 = f2z_sub(ss2(tcc), f2z_mul(tca, tca));
+                const f2_t rr = ss2(sp.w);
+                float a0, a1, e0, e1, f0, f1, n0, n1;
+                f2_unpack(tca, a0, a1); f2_unpack(d2, e0, e1);
+                f2_unpack(f2z_add(tca, rr), f0, f1); f2_unpack(f2z_sub(tca, rr), n0, n1);
+                if (sphere_tail(a0, tcc, e0, f0, n0, r2, t_min, tA) > 0.0f) hA = true;
+                if (sphere_tail(a1, tcc, e1, f1, n1, r2, t_min, tB) > 0.0f) hB = true;
+            }
+        }
+        // bounds as the bits of t_max - t_min (scan_small_native: TRT_V_SHIFT_T); 0 accepts nothing
+        const unsigned cA = tA > t_min ? __float_as_uint(tA - t_min) : 0u, cB = tB > t_min ? __float_as_uint(tB - t_min) : 0u;
+        if (n_pl > 0) {
+            const float nan = __int_as_float(0x7fc00000);
+            const float3 iA = f3(fabsf(dA.x) >= 0.0001f ? rcp_native(dA.x) : nan, fabsf(dA.y) >= 0.0001f ? rcp_native(dA.y) : nan,
+                                 fabsf(dA.z) >= 0.0001f ? rcp_native(dA.z) : nan);
+            const float3 iB = f3(fabsf(dB.x) >= 0.0001f ? rcp_native(dB.x) : nan, fabsf(dB.y) >= 0.0001f ? rcp_native(dB.y) : nan,
+                                 fabsf(dB.z) >= 0.0001f ? rcp_native(dB.z) : nan);
+            const f2_t IX = f2_pack(iA.x, iB.x), IY = f2_pack(iA.y, iB.y), IZ = f2_pack(iA.z, iB.z);
+            // -(o * inv + t_min), the offset of every axis-aligned plane's t'
+            const f2_t NX = f2z_sub(f2z_mul(ss2(-o.x), IX), ss2(t_min)), NY = f2z_sub(f2z_mul(ss2(-o.y), IY), ss2(t_min)),
+                       NZ = f2z_sub(f2z_mul(ss2(-o.z), IZ), ss2(t_min));
+#pragma unroll
+            for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NP : TRT_STATIC_P); j++) {
+                if (j < n_pl) {
+                    const float4 p = c_small.pl_p[j];
+                    const int kind = SHAPE::kFixed ? SHAPE::kind(j) : __float_as_int(p.w);
+                    float t0, t1;
+                    if (kind == 0) f2_unpack(f2z_fma(ss2(p.x), IX, NX), t0, t1);
+                    else if (kind == 1) f2_unpack(f2z_fma(ss2(p.y), IY, NY), t0, t1);
+                    else if (kind == 2) f2_unpack(f2z_fma(ss2(p.z), IZ, NZ), t0, t1);
+                    else {
+                        const float3 n = xyz(c_small.pl_n[j]);
+                        const float num = V::dot(V::sub(xyz(p), o), n);
+                        const float dnA = V::dot(n, dA), dnB = V::dot(n, dB);
+                        t0 = num * (fabsf(dnA) >= 0.0001f ? rcp_native(dnA) : nan) - t_min;
+                        t1 = num * (fabsf(dnB) >= 0.0001f ? rcp_native(dnB) : nan) - t_min;
+                    }
+                    if (__float_as_uint(t0) < cA) hA = true;
+                    if (__float_as_uint(t1) < cB) hB = true;
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < (SHAPE::kFixed ? SHAPE::NT : TRT_STATIC_T); j++) {
+            if (j < n_tri) {
+                // hit_triangle (shader.wgsl:192-223) per ray, the zero-folded form of scan_small_native
+                const unsigned z = SHAPE::tri_zero(j);
+                const bool e1x0 = z & 1u, e1y0 = z & 2u, e1z0 = z & 4u, e2x0 = z & 8u, e2y0 = z & 16u, e2z0 = z & 32u;
+                const float3 e1 = xyz(c_small.tri_e1[j]), e2 = xyz(c_small.tri_e2[j]);
+                const float3 s = V::sub(o, xyz(c_small.tri_v0[j]));
+                const float3 q = f3(dpz(s.y, e1.z, e1z0, s.z, e1.y, e1y0), dpz(s.z, e1.x, e1x0, s.x, e1.z, e1z0),
+                                    dpz(s.x, e1.y, e1y0, s.y, e1.x, e1x0));                   // cross(s, e1): the same for both rays
+                const bool qx0 = e1z0 && e1y0, qy0 = e1x0 && e1z0, qz0 = e1y0 && e1x0;
+                const float e2q = dotz(e2, q, e2x0 || qx0, e2y0 || qy0, e2z0 || qz0);
+                const bool hx0 = e2z0 && e2y0, hy0 = e2x0 && e2z0, hz0 = e2y0 && e2x0;
+                auto one = [&](float3 rd, unsigned cb) -> bool {
+                    const float3 h = f3(dpz(rd.y, e2.z, e2z0, rd.z, e2.y, e2y0), dpz(rd.z, e2.x, e2x0, rd.x, e2.z, e2z0),
+                                        dpz(rd.x, e2.y, e2y0, rd.y, e2.x, e2x0));                       // cross(rd, e2)
+                    const float a = dotz(e1, h, e1x0 || hx0, e1y0 || hy0, e1z0 || hz0);
+                    if (a > -0.00001f && a < 0.00001f) return false;
+                    const float f = rcp_native(a);
+                    const float u = f * dotz(s, h, hx0, hy0, hz0);
+                    if (u < 0.0f || u > 1.0f) return false;
+                    const float v = f * dotz(rd, q, qx0, qy0, qz0);
+                    if (v < 0.0f || u + v > 1.0f) return false;
+                    const float t = f * e2q;
+                    return __float_as_uint(t - t_min) < cb;
+                };
+                if (one(dA, cA)) hA = true;
+                if (one(dB, cB)) hB = true;
+            }
+        }
+        occA = hA;
+        occB = hB;
+    }
+#endif
+
     // any-hit form of the same scan for shadow rays: only `hit.t < 0` is read by the caller
     // (shader.wgsl:400-402), and before the first accepted hit the bound is still t_max, so stopping at
     // the first accepted primitive returns the same truth value.
