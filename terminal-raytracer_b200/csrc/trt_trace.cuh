@@ -536,17 +536,35 @@ struct Tracer {
         const f2_t k2 = f2_pack(1.0f - 2e-5f, 1.0f - 2e-5f);
         const ulonglong2 *d = reinterpret_cast<const ulonglong2 *>(acc.d);
         const int n_pairs = (run.z - run.y) >> 1;
-#pragma unroll 2
-        for (int p = 0; p < n_pairs; p++) {
+        // (lhs, rhs) of the inequality for the two primitives of pair p: far away <=> lhs > rhs
+        auto pair_test = [&](int p, float &l0, float &l1, float &r0, float &r1) {
             const ulonglong2 q0 = d[2 * p], q1 = d[2 * p + 1];
             const f2_t tcx = f2_add(q0.x, nrx), tcy = f2_add(q0.y, nry), tcz = f2_add(q1.x, nrz);
             const f2_t tca = f2_fma(tcz, dz, f2_fma(tcy, dy, f2_mul(tcx, dx)));
             const f2_t tcc = f2_fma(tcz, tcz, f2_fma(tcy, tcy, f2_mul(tcx, tcx)));
-            float l0, l1, r0, r1;
             f2_unpack(f2_fma(tcc, k2, q1.y), l0, l1);
             f2_unpack(f2_mul(tca, tca), r0, r1);
-            if (!(l0 > r0)) full(run.y + 2 * p);
-            if (!(l1 > r1)) full(run.y + 2 * p + 1);
+        };
+        int p = 0;
+        // two pairs per round, ONE branch for the four primitives in the common case (all four far away for all lanes)
+        for (; p + 2 <= n_pairs; p += 2) {
+            float a0, a1, b0, b1, c0, c1, e0, e1;
+            pair_test(p, a0, a1, b0, b1);
+            pair_test(p + 1, c0, c1, e0, e1);
+            if (!(a0 > b0 && a1 > b1 && c0 > e0 && c1 > e1)) {
+                if (!(a0 > b0)) full(run.y + 2 * p);
+                if (!(a1 > b1)) full(run.y + 2 * p + 1);
+                if (!(c0 > e0)) full(run.y + 2 * p + 2);
+                if (!(c1 > e1)) full(run.y + 2 * p + 3);
+            }
+        }
+        for (; p < n_pairs; p++) {
+            float l0, l1, r0, r1;
+            pair_test(p, l0, l1, r0, r1);
+            if (!(l0 > r0 && l1 > r1)) {
+                if (!(l0 > r0)) full(run.y + 2 * p);
+                if (!(l1 > r1)) full(run.y + 2 * p + 1);
+            }
         }
         int i = run.y + 2 * n_pairs;
         if (run.x == 2)
