@@ -259,3 +259,24 @@ def test_large_scene_native_deferred_kernel(pkg, O):
     g6, _, _, _ = _render(pkg, prims, u6, 96, 54, 2)
     print(f"  depth 6: native-vs-strict RMSE {_rmse(g6, a):.4g}, noise floor {_rmse(a, b):.4g}")
     assert _rmse(g6, a) <= 0.08 * _rmse(a, b)
+
+
+def test_full_c4_scene_cull_keeps_every_hit(pkg, O):
+    """All 20 484 primitives, single bounce: the large-scene kernel culls triangles and spheres by a distance test on packed
+    pairs before the as-written tests (scan_run / tri_cull, two primitives per step, one branch per four).  A cull that
+    dropped a real hit would put sky or a farther primitive into a pixel -- a whole-sample flip.  The yardstick is the
+    strict machine itself (no cull there): its two exact conventions against each other, both on the GPU."""
+    sc = O.make_c4_scene()
+    prims = O.flatten_scene(sc)
+    assert len(prims) == 20484
+    w, h = 160, 90
+    u = O.make_uniforms(sc, len(prims), O.C4_SEED, 0, width=w, height=h, spp=4, max_depth=1)
+    s0, _, _, _ = _render(pkg, prims, u, w, h, 0)
+    s1, _, _, _ = _render(pkg, prims, u, w, h, 1)
+    r = pkg.Renderer(w, h, conv=2)
+    r.upload_scene(prims)
+    r.render_frame(_u(pkg, u), pkg.MODE_NONE)
+    got, kernel = r.read_pixels(), r.kernel_name()
+    r.close()
+    assert "SrcTiled" in kernel
+    _assert_within_conventions(f"C4 full scene, depth 1, {kernel}", got, s0, s1, w, h)
