@@ -205,8 +205,11 @@ __global__ void __launch_bounds__(TRT_Q_BLOCK) quant_emit_kernel(QuantParams q) 
 #ifndef TRT_QF_PER_THREAD
 #define TRT_QF_PER_THREAD 4
 #endif
+// resident CTAs the register allocation must allow.  The kernel is bound by the latency of a tile's dependent phases (load,
+// scan, format, look-back, copy-out), so tiles in flight count: 1 (62 registers, 4 CTAs) 0.234 ms on a 3840x2160 frame,
+// 5 (48 registers) 0.203 ms, 6 (40 registers, spills) 0.200-0.207 ms, 7 (32 registers) 0.208-0.213 ms (profiles/r2_quant_fused_raw.txt)
 #ifndef TRT_QF_MIN_CTAS
-#define TRT_QF_MIN_CTAS 1
+#define TRT_QF_MIN_CTAS 5
 #endif
 #define TRT_QF_TILE (TRT_Q_BLOCK * TRT_QF_PER_THREAD)
 #define TRT_QF_STAGE (TRT_QF_TILE * 28 + 32)

@@ -94,14 +94,14 @@ def test_runtime_specialisation_compiles(shape, what, tmp_path):
             b"-diag-suppress=177"]
     err, = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
     _, n = nvrtc.nvrtcGetProgramLogSize(prog)
-    log = b" " * n
+    log = bytes(n + 16)        # NVRTC writes into it: never a length-0 / length-1 bytes object, CPython shares those
     nvrtc.nvrtcGetProgramLog(prog, log)
     assert err == nvrtc.nvrtcResult.NVRTC_SUCCESS, log.decode(errors="replace")
     _, n = nvrtc.nvrtcGetCUBINSize(prog)
-    cubin = b" " * n
+    cubin = bytes(n + 16)
     nvrtc.nvrtcGetCUBIN(prog, cubin)
     path = tmp_path / "jit.cubin"
-    path.write_bytes(cubin)
+    path.write_bytes(cubin[:n])
     res = _res_usage(str(path))
     assert list(res) == ["trt_jit_trace"]
     r = res["trt_jit_trace"]

@@ -20,14 +20,14 @@ def compile_shape(shape="ShapeFixed<3, 6, 2, 0xa05u, 2, 0x0u, 0x4deu>", extra=()
             b"-diag-suppress=177"] + [e.encode() for e in extra]
     err, = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
     _, n = nvrtc.nvrtcGetProgramLogSize(prog)
-    log = b" " * n
+    log = bytes(n + 16)        # NVRTC writes into it: never a length-0 / length-1 bytes object, CPython shares those
     nvrtc.nvrtcGetProgramLog(prog, log)
     if err != nvrtc.nvrtcResult.NVRTC_SUCCESS:
         raise RuntimeError(log.decode(errors="replace"))
     _, n = nvrtc.nvrtcGetCUBINSize(prog)
-    cubin = b" " * n
+    cubin = bytes(n + 16)
     nvrtc.nvrtcGetCUBIN(prog, cubin)
-    return cubin, log.decode(errors="replace").strip("\x00 \n")
+    return cubin[:n], log.decode(errors="replace").strip("\x00 \n")
 
 
 if __name__ == "__main__":
