@@ -735,7 +735,11 @@ static int trace_impl(trt_ctx *ctx, const trt_uniforms *u, uint32_t n_batch) {
     }
     // longest pixels first, predicted by the variance buffer of the previous frame of the same size
     static const bool no_order = [] { const char *k = getenv("TRT_B200_NO_ORDER"); return k && *k == '1'; }();
-    if (!no_order && !n_batch && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
+    // (not for frames far smaller than the machine: with fewer pixels than two lanes per SM-resident warp slot every pixel
+    // starts at once whatever the order, and the two sorting launches are 5 % of a 0.3 ms frame -- C5: p50 0.298 -> 0.281 ms;
+    // C1's 80 000 pixels still gain 1.7 % from warps of like pixels)
+    const bool worth_ordering = fp.n_local_pixels > 2u * (uint32_t)ctx->sm_count * 128u;
+    if (!no_order && worth_ordering && !n_batch && !ctx->cfg.count_work && fp.n_local_pixels && ctx->order_w == u->width && ctx->order_h == u->height) {
         CK(cudaMemsetAsync(ctx->d_work + 16, 0, 2 * TRT_ORDER_BUCKETS * sizeof(unsigned int), ctx->stream));
         const uint32_t ob = (fp.n_local_pixels + 255u) / 256u;
         const uint32_t *cost = ctx->cost_valid ? ctx->d_cost : nullptr;
